@@ -1,0 +1,199 @@
+/*
+ * psim.h — C ABI of the B200-native Lennard-Jones / Stoermer-Verlet hot path.
+ *
+ * The reference (RobertOpitz/Particle_simulation) has no FFI or plugin interface
+ * of its own: its integrator module takes assumed-shape arrays of a
+ * non-interoperable derived type (fortran_src/module_stoermer_verlet_method.f08:16-27,
+ * :87-88, :136-137, :191-192).  This header is therefore the interface a
+ * maintainer binds with ISO_C_BINDING (see INTEGRATION.md and
+ * particle_simulation_b200/fortran/psim_binding.f08).  Each entry point names
+ * the reference procedure(s) it stands in for.
+ *
+ * Conventions
+ *   - every function returns a psim_status (0 = success) and never aborts;
+ *   - all pointers are plain host pointers unless a name ends in _dev;
+ *   - `precision` is the byte width of the real type, 4 (the reference's
+ *     `rt => real32`, module_stoermer_verlet_method.f08:5) or 8; real arrays are
+ *     passed as `const void*` / `void*` and hold float or double accordingly;
+ *   - vectors are packed xyz, particle-major: pos[3*i + 0..2];
+ *   - one host thread per handle; the library owns all device memory and streams;
+ *   - there is no CPU fallback: without a CUDA device every call that would
+ *     compute returns PSIM_ERR_NO_DEVICE.
+ */
+#ifndef PSIM_H
+#define PSIM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum psim_status {
+  PSIM_OK = 0,
+  PSIM_ERR_INVALID_ARGUMENT = 1,
+  PSIM_ERR_NO_DEVICE = 2,
+  PSIM_ERR_CUDA = 3,
+  PSIM_ERR_NO_PARTICLES = 4,   /* "No particles in particle file", program_particle_simulation_openmp.f08:269-270 */
+  PSIM_ERR_UNSUPPORTED = 5,
+  PSIM_ERR_COMM = 6,
+  PSIM_ERR_IO = 7
+} psim_status;
+
+/* The ten namelist keys of ENVIRONMENTPARAMS
+ * (program_particle_simulation_openmp.f08:198-200; environment_params.nml:2-11)
+ * minus the two that only drive the time loop (write/max time step are
+ * arguments of psim_run).  Values are held in double and rounded once to the
+ * working precision, then the derived constants are formed in that precision
+ * in the reference's expression order (module_stoermer_verlet_method.f08:68-81). */
+typedef struct psim_params {
+  double delta_t;            /* DELTA_T */
+  double epsilon;            /* EPSILON  -> input_epsilon_value (program_...:219-220) */
+  double sigma;              /* SIGMA    -> particle_radius */
+  double mass;               /* MASS     -> particle_mass */
+  double r_cut_factor;       /* R_CUT    -> r_cut_factor (r_cut = R_CUT * SIGMA) */
+  double length_of_area[3];  /* LENGTH_OF_AREA */
+  double length_of_cell[3];  /* LENGTH_OF_CELL */
+  int32_t nb_of_threads;     /* NB_OF_THREADS: the reference evaluates its
+                                rebuild trigger per thread slice
+                                (program_...:71,86,92; slices :305-323); the
+                                device reproduces that per-slice trigger.  <=0 means 1. */
+  int32_t reserved;
+} psim_params;
+
+/* Force evaluation strategy (all give the same forces up to summation order). */
+typedef enum psim_force_algo {
+  PSIM_FORCE_ALL_PAIRS = 0,  /* tiled all-pairs scan, N(N-1) ordered pair tests per step */
+  PSIM_FORCE_CELL_BINNED = 1 /* particles binned by LENGTH_OF_CELL, 27-cell neighbourhood
+                                (what module_particle_management.f08:52-108,179-339 achieves with lists) */
+} psim_force_algo;
+
+typedef enum psim_option {
+  PSIM_OPT_FORCE_ALGO = 0,      /* psim_force_algo */
+  PSIM_OPT_FUSED_STEP = 1,      /* 1: force+kick+drift in one kernel (default), 0: separate kernels */
+  PSIM_OPT_KERNEL_TIMING = 2,   /* 1: bracket every force-kernel launch with CUDA events */
+  PSIM_OPT_EXACT_DIFF_FILTER = 3 /* 1: all-pairs distance test in difference form (7 pipe ops/pair)
+                                    instead of the norm-expansion pre-filter (3 FMAs/pair) */
+} psim_option;
+
+typedef struct psim_counters {
+  int64_t steps;            /* time steps advanced since create */
+  int64_t rebuilds;         /* times the reference's rebuild trigger fired */
+  int64_t kernel_launches;  /* kernels of this library launched since create */
+  int64_t force_launches;   /* of which force kernels */
+  double  force_ms;         /* summed device time of timed force launches (PSIM_OPT_KERNEL_TIMING) */
+  int64_t force_timed;      /* number of force launches that were timed */
+  int64_t n_active;         /* active particles after the last completed step */
+} psim_counters;
+
+typedef struct psim_sim psim_sim;   /* opaque */
+
+/* --- life cycle --------------------------------------------------------- */
+
+/* Replaces: set_simulation_parameter (module_stoermer_verlet_method.f08:52-83),
+ * the particle-array fill (program_...:226-286), initialize_neighbor_lists'
+ * observable effect (particles outside the box start inactive,
+ * module_particle_management.f08:82-92, 534-552) and the initial
+ * compute_forces call (program_...:77).
+ * id[n], pos[3n], vel[3n] are caller-owned host arrays and are copied.
+ * device < 0 selects the current CUDA device. */
+psim_status psim_create(const psim_params* params, int precision, int64_t n,
+                        const int32_t* id, const void* pos, const void* vel,
+                        int device, psim_sim** out);
+
+/* Multi-GPU create: this process owns the contiguous i-slice `rank` of
+ * `world` (the reference's thread slices, program_...:305-323, one per GPU).
+ * All ranks pass the full particle arrays.  nccl_unique_id is the 128-byte
+ * ncclUniqueId produced by psim_comm_unique_id on rank 0 and distributed by the
+ * host (torch.distributed, MPI, a file ...). */
+psim_status psim_create_sharded(const psim_params* params, int precision, int64_t n,
+                                const int32_t* id, const void* pos, const void* vel,
+                                int device, int rank, int world,
+                                const void* nccl_unique_id, psim_sim** out);
+psim_status psim_comm_unique_id(void* out128);
+
+/* Replaces: clean_up (module_particle_management.f08:556-598). */
+psim_status psim_destroy(psim_sim* sim);
+
+psim_status psim_set_option(psim_sim* sim, int option, int64_t value);
+
+/* --- the time loop ------------------------------------------------------ */
+
+/* Replaces one or more trips of the time_integration loop
+ * (program_...:80-117): compute_locations -> rebuild side effects ->
+ * compute_forces -> compute_velocities, nsteps times.  Asynchronous: returns
+ * once the work is enqueued.  psim_synchronize waits. */
+psim_status psim_advance(psim_sim* sim, int64_t nsteps);
+psim_status psim_synchronize(psim_sim* sim);
+
+/* As psim_advance but bracketed by CUDA events on the library's own stream;
+ * returns the device time of the nsteps in milliseconds (synchronous). */
+psim_status psim_advance_timed(psim_sim* sim, int64_t nsteps, double* elapsed_ms);
+
+/* --- reading state back -------------------------------------------------- */
+
+/* Replaces the data gathered by write_data (program_...:327-365): id, location,
+ * velocity and the active flag of all n particles in array order (the host
+ * filters inactive ones, as write_data does at :342).  Any pointer may be NULL.
+ * Synchronous. */
+psim_status psim_get_frame(psim_sim* sim, int32_t* id, void* pos, void* vel,
+                           uint8_t* active);
+
+/* Test/diagnostic access to the rest of particle_type
+ * (module_stoermer_verlet_method.f08:19-23): displacement, force_old, force_new. */
+psim_status psim_get_aux(psim_sim* sim, void* displacement, void* force_old,
+                         void* force_new);
+
+psim_status psim_get_counters(psim_sim* sim, psim_counters* out);
+
+/* Frame ring for the output cadence (program_...:109-115): snapshot the
+ * current (post-kick) state into pinned slot `slot` (0..PSIM_FRAME_SLOTS-1) by
+ * async D2H on a side stream, without stalling the stepping stream; then wait
+ * for a slot and get pointers into the pinned buffers (valid until the slot is
+ * snapshotted again).  pos/vel point at `precision`-byte reals, packed xyz. */
+#define PSIM_FRAME_SLOTS 4
+psim_status psim_snapshot_async(psim_sim* sim, int slot);
+psim_status psim_snapshot_wait(psim_sim* sim, int slot, const int32_t** id,
+                               const void** pos, const void** vel,
+                               const uint8_t** active);
+
+/* --- the force operator on its own --------------------------------------- */
+
+/* Replaces: compute_forces + compute_force_between_two_particles
+ * (module_stoermer_verlet_method.f08:87-132) as a stateless operator over host
+ * arrays: force[3n] = sum over active j != i with r < r_cut.  active may be
+ * NULL (all active).  Includes the H2D and D2H copies.  pairs_in_range (may be
+ * NULL) receives the number of ordered pairs inside the cutoff. */
+psim_status psim_compute_forces_host(const psim_params* params, int precision,
+                                     int64_t n, const void* pos,
+                                     const uint8_t* active, int algo, int device,
+                                     void* force, int64_t* pairs_in_range);
+
+/* Ordered pairs (i, j != i), both active, with r < r_cut at the current
+ * positions (P_in).  Synchronous. */
+psim_status psim_count_pairs_in_range(psim_sim* sim, int64_t* pairs);
+
+/* Total kinetic and potential energy and linear momentum of the active
+ * particles, accumulated in double.  The reference computes neither; the
+ * potential is the one whose gradient is its force. */
+psim_status psim_energy(psim_sim* sim, double* kinetic, double* potential,
+                        double momentum[3]);
+
+/* --- measurement helpers ------------------------------------------------- */
+
+/* Dependent-free FMA loop on every SM: the measured FMA-pipe peak of this GPU
+ * in TFLOP/s for `precision` 4 or 8 (MEASURED_PEAKS.json holds no FP64/FP32
+ * vector figure).  sm_mhz (may be NULL) receives the SM clock derived from
+ * clock64() over the run. */
+psim_status psim_measure_fma_peak(int precision, int device, double* tflops,
+                                  double* sm_mhz);
+
+const char* psim_status_string(int status);
+/* Text of the last CUDA/NCCL error seen by this thread ("" if none). */
+const char* psim_last_error(void);
+const char* psim_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSIM_H */
