@@ -146,6 +146,20 @@ psim_status psim_get_aux(psim_sim* sim, void* displacement, void* force_old,
 
 psim_status psim_get_counters(psim_sim* sim, psim_counters* out);
 
+/* The half-open range of particle indices this handle owns (0..n for a
+ * single-GPU handle).  In a sharded run psim_get_frame / psim_get_aux /
+ * snapshots fill velocity, force and displacement for this range only
+ * (positions and active flags are complete on every rank); the host
+ * concatenates ranks in order, which is array order. */
+psim_status psim_get_shard(psim_sim* sim, int64_t* i_lo, int64_t* i_hi);
+
+/* Replace all positions (host array pos[3n]), redo the start-up activation
+ * (or take `active`, if not NULL), zero displacement and forces, and evaluate
+ * the forces at the new positions, i.e. compute_forces as at
+ * program_...:77.  With psim_get_aux(force_new) this is the force operator
+ * on a resident handle: no allocation per call. */
+psim_status psim_set_positions(psim_sim* sim, const void* pos, const uint8_t* active);
+
 /* Frame ring for the output cadence (program_...:109-115): snapshot the
  * current (post-kick) state into pinned slot `slot` (0..PSIM_FRAME_SLOTS-1) by
  * async D2H on a side stream, without stalling the stepping stream; then wait

@@ -1,0 +1,746 @@
+// psim_api.cu — the C ABI of include/psim.h over the kernels in this directory.
+//
+// One psim_sim owns one CUDA device context's worth of state: double-buffered
+// position records, velocity / force / displacement records for the owned
+// i-slice, a device-resident control block for the rebuild trigger, a frame
+// ring of pinned host buffers, and (sharded runs) an NCCL communicator.
+// Nothing here falls back to the CPU: without a device every compute entry
+// point returns PSIM_ERR_NO_DEVICE.
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "psim_allpairs.cuh"
+#include "psim_cells.cuh"
+#include "psim_integrate.cuh"
+
+namespace psim {
+
+static thread_local std::string g_last_error;
+
+#define PSIM_CK(call)                                                                  \
+  do {                                                                                 \
+    cudaError_t e_ = (call);                                                           \
+    if (e_ != cudaSuccess) {                                                           \
+      g_last_error = std::string(#call) + ": " + cudaGetErrorString(e_);               \
+      return e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? PSIM_ERR_NO_DEVICE : PSIM_ERR_CUDA; \
+    }                                                                                  \
+  } while (0)
+
+// ---- NCCL, bound lazily so that single-GPU users never load it -------------
+struct NcclApi {
+  void* so = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  bool load() {
+    if (so) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+      so = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (so) break;
+    }
+    if (!so) { g_last_error = std::string("dlopen libnccl: ") + dlerror(); return false; }
+#define BIND(f) f = (decltype(f))dlsym(so, "nccl" #f); if (!f) { g_last_error = "dlsym nccl" #f; return false; }
+    BIND(GetUniqueId) BIND(CommInitRank) BIND(CommDestroy) BIND(AllGather) BIND(GroupStart) BIND(GroupEnd)
+    BIND(GetErrorString)
+#undef BIND
+    return true;
+  }
+};
+static NcclApi g_nccl;
+
+#define PSIM_NCCL(call)                                                                \
+  do {                                                                                 \
+    ncclResult_t r_ = (call);                                                          \
+    if (r_ != ncclSuccess) {                                                           \
+      g_last_error = std::string(#call) + ": " + g_nccl.GetErrorString(r_);            \
+      return PSIM_ERR_COMM;                                                            \
+    }                                                                                  \
+  } while (0)
+
+template <class R> struct NcclType;
+template <> struct NcclType<float>  { static constexpr ncclDataType_t v = ncclFloat; };
+template <> struct NcclType<double> { static constexpr ncclDataType_t v = ncclDouble; };
+
+// stoermer:68-81 on the host in working precision R, plus the pre-filter margins.
+template <class R>
+static Consts<R> derive_consts(const psim_params& p) {
+  Consts<R> c;
+  const R sigma = (R)p.sigma, mass = (R)p.mass, rcf = (R)p.r_cut_factor;
+  c.delta_t = (R)p.delta_t;
+  c.epsilon = (R)p.epsilon;
+  c.r_min = std::pow((R)2, (R)1 / (R)6) * sigma;
+  c.r_cut = rcf * sigma;
+  for (int d = 0; d < 3; ++d) {
+    c.area[d] = (R)p.length_of_area[d];
+    c.cell[d] = (R)p.length_of_cell[d];
+    c.nc[d] = (int)std::lround(c.area[d] / c.cell[d]);     // nint, module_particle_management.f08:62
+  }
+  c.min_cell = std::min(c.cell[0], std::min(c.cell[1], c.cell[2]));
+  c.dr_max_tolerable = c.min_cell - c.r_cut;
+  // the host compiler targets baseline x86-64 (no FMA contraction), so these
+  // round once per operation exactly like the oracle's -ffp-contract=off build
+  const R q = c.r_min / c.r_cut;
+  const R q2 = q * q;
+  const R s = q2 * q2 * q2;
+  c.F_rcut = (s / (c.r_cut * c.r_cut)) * ((R)1 - s);
+  c.tmf = (R)0.5 * c.delta_t / mass;
+  const R eps = RealTraits<R>::unit_roundoff;
+  c.one_minus_k = (R)1 - (R)32 * eps;
+  c.cut2_pad = c.r_cut * c.r_cut * ((R)1 + (R)32 * eps);
+  c.huge = RealTraits<R>::huge;
+  c.slices = std::max<int>(1, p.nb_of_threads);
+  return c;
+}
+
+}  // namespace psim
+
+using namespace psim;
+
+// ---------------------------------------------------------------------------
+struct psim_sim {
+  virtual ~psim_sim() {}
+  virtual psim_status advance(int64_t nsteps) = 0;
+  virtual psim_status advance_timed(int64_t nsteps, double* ms) = 0;
+  virtual psim_status synchronize() = 0;
+  virtual psim_status get_frame(int32_t* id, void* pos, void* vel, uint8_t* active) = 0;
+  virtual psim_status get_aux(void* disp, void* f_old, void* f_new) = 0;
+  virtual psim_status get_counters(psim_counters* out) = 0;
+  virtual psim_status set_option(int opt, int64_t value) = 0;
+  virtual psim_status set_positions(const void* pos, const uint8_t* active) = 0;
+  virtual psim_status snapshot_async(int slot) = 0;
+  virtual psim_status snapshot_wait(int slot, const int32_t** id, const void** pos, const void** vel,
+                                    const uint8_t** active) = 0;
+  virtual psim_status count_pairs(int64_t* pairs) = 0;
+  virtual psim_status energy(double* k, double* u, double* mom) = 0;
+  virtual psim_status get_shard(int64_t* lo, int64_t* hi) = 0;
+};
+
+namespace psim {
+
+template <class R>
+class SimT final : public psim_sim {
+ public:
+  static constexpr int T = 128;                                   // threads per force block = j-tile
+  static constexpr int RI = 2;                                    // i-particles per thread
+  static constexpr int TS = 256;                                  // threads of the streaming kernels
+
+  int device = 0;
+  int64_t n = 0, n_pad = 0, shard = 0, i_lo = 0, i_hi = 0;
+  int rank = 0, world = 1;
+  Consts<R> c;
+  double mass = 1.0;
+  cudaStream_t stream = nullptr, side = nullptr;
+  Real4<R>* pos[2] = {nullptr, nullptr};
+  int cur = 0;
+  Real4<R>*vel = nullptr, *f_old = nullptr, *f_new = nullptr, *disp = nullptr;
+  R* top2_part = nullptr;
+  int64_t top2_cap = 0, top2_count = 0;
+  R* top2_rank = nullptr;       // [2 * world]
+  Control* ctrl = nullptr;
+  int parity = 0;
+  bool pending_drift = false;   // the previous fused kernel already produced x_{n+1}
+  std::vector<int32_t> ids;
+  R* tmp3 = nullptr;            // [3 * n_pad] scratch for pack/unpack
+  unsigned char* tmp_active = nullptr;
+  CellPath<R> cells;
+  // options
+  int algo = PSIM_FORCE_ALL_PAIRS;
+  bool fused = true, timing = false, exact_diff = false;
+  // counters
+  int64_t steps = 0, launches = 0, force_launches = 0, force_timed = 0;
+  double force_ms = 0.0;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
+  size_t ev_used = 0;
+  // frame ring
+  struct Slot { R* d_pos = nullptr; R* d_vel = nullptr; unsigned char* d_act = nullptr;
+                R* h_pos = nullptr; R* h_vel = nullptr; unsigned char* h_act = nullptr;
+                cudaEvent_t ready = nullptr, done = nullptr; bool used = false; };
+  Slot slots[PSIM_FRAME_SLOTS];
+  ncclComm_t comm = nullptr;
+
+  ~SimT() override { destroy(); }
+
+  void destroy() {
+    if (device >= 0) cudaSetDevice(device);
+    if (stream) cudaStreamSynchronize(stream);
+    if (side) cudaStreamSynchronize(side);
+    if (comm) { g_nccl.CommDestroy(comm); comm = nullptr; }
+    cells.destroy();
+    for (auto& s : slots) {
+      cudaFree(s.d_pos); cudaFree(s.d_vel); cudaFree(s.d_act);
+      cudaFreeHost(s.h_pos); cudaFreeHost(s.h_vel); cudaFreeHost(s.h_act);
+      if (s.ready) cudaEventDestroy(s.ready);
+      if (s.done) cudaEventDestroy(s.done);
+      s = Slot();
+    }
+    for (auto& e : ev_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    ev_pool.clear();
+    cudaFree(pos[0]); cudaFree(pos[1]); cudaFree(vel); cudaFree(f_old); cudaFree(f_new); cudaFree(disp);
+    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active);
+    pos[0] = pos[1] = vel = f_old = f_new = disp = nullptr;
+    top2_part = top2_rank = nullptr; ctrl = nullptr; tmp3 = nullptr; tmp_active = nullptr;
+    if (stream) cudaStreamDestroy(stream);
+    if (side) cudaStreamDestroy(side);
+    stream = side = nullptr;
+  }
+
+  static int64_t blocks(int64_t count, int per) { return (count + per - 1) / per; }
+
+  psim_status init(const psim_params& p, int64_t n_, const int32_t* id, const void* pos_h, const void* vel_h,
+                   const uint8_t* active_h, int device_, int rank_, int world_, const void* uid) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+      g_last_error = std::string("no CUDA device: ") + cudaGetErrorString(e);
+      cudaGetLastError();
+      return PSIM_ERR_NO_DEVICE;
+    }
+    if (device_ < 0) PSIM_CK(cudaGetDevice(&device_));
+    device = device_;
+    PSIM_CK(cudaSetDevice(device));
+    n = n_; rank = rank_; world = world_;
+    c = derive_consts<R>(p);
+    mass = p.mass;
+    if (!(c.min_cell >= c.r_cut)) {
+      // the reference's lists would then drop pairs inside the cutoff
+      // (module_particle_management.f08:384 keeps r <= min_length_of_cell only)
+      g_last_error = "LENGTH_OF_CELL smaller than R_CUT*SIGMA is not supported";
+      return PSIM_ERR_UNSUPPORTED;
+    }
+    const int64_t gran = (int64_t)T * world;
+    n_pad = (n + gran - 1) / gran * gran;
+    shard = n_pad / world;
+    i_lo = std::min<int64_t>(n, shard * rank);
+    i_hi = std::min<int64_t>(n, shard * (rank + 1));
+    PSIM_CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    PSIM_CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+    const size_t rec = sizeof(Real4<R>) * (size_t)n_pad;
+    PSIM_CK(cudaMalloc(&pos[0], rec)); PSIM_CK(cudaMalloc(&pos[1], rec));
+    PSIM_CK(cudaMalloc(&vel, rec)); PSIM_CK(cudaMalloc(&f_old, rec));
+    PSIM_CK(cudaMalloc(&f_new, rec)); PSIM_CK(cudaMalloc(&disp, rec));
+    top2_cap = std::max<int64_t>(blocks(n_pad, TS), blocks(n_pad, T)) + 8;
+    PSIM_CK(cudaMalloc(&top2_part, sizeof(R) * 2 * top2_cap));
+    PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * world));
+    PSIM_CK(cudaMalloc(&ctrl, sizeof(Control)));
+    PSIM_CK(cudaMemsetAsync(ctrl, 0, sizeof(Control), stream));
+    PSIM_CK(cudaMalloc(&tmp3, sizeof(R) * 3 * n_pad));
+    PSIM_CK(cudaMalloc(&tmp_active, (size_t)n_pad));
+    ids.assign(id, id + n);
+    if (world > 1) {
+      if (!g_nccl.load()) return PSIM_ERR_COMM;
+      ncclUniqueId nid;
+      std::memcpy(&nid, uid, sizeof nid);
+      PSIM_NCCL(g_nccl.CommInitRank(&comm, world, nid, rank));
+    }
+    // velocities, then positions + initial activation + initial forces
+    if (vel_h) PSIM_CK(cudaMemcpyAsync(tmp3, vel_h, sizeof(R) * 3 * n, cudaMemcpyHostToDevice, stream));
+    unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(vel, vel_h ? tmp3 : nullptr, n, n_pad); ++launches;
+    PSIM_CK(cudaStreamSynchronize(stream));   // tmp3 is reused below
+    psim_status st = set_positions(pos_h, active_h);
+    if (st != PSIM_OK) return st;
+    return PSIM_OK;
+  }
+
+  // Upload positions, redo the start-up activation, zero displacement and
+  // forces, and evaluate the initial forces (program_...:77).
+  psim_status set_positions(const void* pos_h, const uint8_t* active_h) override {
+    PSIM_CK(cudaSetDevice(device));
+    if (!pos_h) return PSIM_ERR_INVALID_ARGUMENT;
+    PSIM_CK(cudaMemcpyAsync(tmp3, pos_h, sizeof(R) * 3 * n, cudaMemcpyHostToDevice, stream));
+    if (active_h) PSIM_CK(cudaMemcpyAsync(tmp_active, active_h, (size_t)n, cudaMemcpyHostToDevice, stream));
+    init_positions_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(pos[0], pos[1], tmp3,
+                                                                     active_h ? tmp_active : nullptr, n, n_pad, c);
+    unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(disp, nullptr, n, n_pad);
+    unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(f_old, nullptr, n, n_pad);
+    unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(f_new, nullptr, n, n_pad);
+    launches += 4;
+    cur = 0; pending_drift = false;
+    cells.invalidate();
+    psim_status st = launch_force(MODE_FORCE);
+    if (st != PSIM_OK) return st;
+    PSIM_CK(cudaGetLastError());
+    return PSIM_OK;
+  }
+
+  StepArgs<R> step_args() const {
+    StepArgs<R> a;
+    a.pos_cur = pos[cur]; a.pos_nxt = pos[cur ^ 1];
+    a.vel = vel; a.f_old = f_old; a.f_new = f_new; a.disp = disp;
+    a.top2_part = top2_part;
+    a.n_pad = n_pad; a.i_lo = i_lo; a.i_hi = i_hi;
+    a.c = c;
+    return a;
+  }
+
+  template <int MODE>
+  void launch_allpairs(const StepArgs<R>& a, int64_t grid) {
+    if (exact_diff) allpairs_step_kernel<R, T, RI, MODE, true><<<grid, T, 0, stream>>>(a);
+    else allpairs_step_kernel<R, T, RI, MODE, false><<<grid, T, 0, stream>>>(a);
+  }
+
+  psim_status launch_force(int mode) {
+    if (i_hi <= i_lo) return PSIM_OK;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (timing) {
+      if (ev_used == ev_pool.size()) {
+        if (ev_pool.size() >= 8192) { psim_status st = drain_events(); if (st != PSIM_OK) return st; }
+        else {
+          cudaEvent_t a, b;
+          PSIM_CK(cudaEventCreate(&a)); PSIM_CK(cudaEventCreate(&b));
+          ev_pool.emplace_back(a, b);
+        }
+      }
+      e0 = ev_pool[ev_used].first; e1 = ev_pool[ev_used].second; ++ev_used;
+      PSIM_CK(cudaEventRecord(e0, stream));
+    }
+    if (algo == PSIM_FORCE_CELL_BINNED) {
+      psim_status st = cells.force(*this, mode);
+      if (st != PSIM_OK) return st;
+    } else {
+      const StepArgs<R> a = step_args();
+      const int64_t grid = blocks(i_hi - i_lo, T * RI);
+      if (mode == MODE_FORCE) launch_allpairs<MODE_FORCE>(a, grid);
+      else if (mode == MODE_FORCE_KICK) launch_allpairs<MODE_FORCE_KICK>(a, grid);
+      else { launch_allpairs<MODE_FORCE_KICK_DRIFT>(a, grid); top2_count = grid; }
+      ++launches;
+    }
+    ++force_launches;
+    if (timing) PSIM_CK(cudaEventRecord(e1, stream));
+    return PSIM_OK;
+  }
+
+  psim_status drain_events() {
+    PSIM_CK(cudaStreamSynchronize(stream));
+    for (size_t k = 0; k < ev_used; ++k) {
+      float ms = 0;
+      PSIM_CK(cudaEventElapsedTime(&ms, ev_pool[k].first, ev_pool[k].second));
+      force_ms += ms; ++force_timed;
+    }
+    ev_used = 0;
+    return PSIM_OK;
+  }
+
+  // After x_{n+1} of the owned slice is in pos[cur^1]: exchange (sharded),
+  // evaluate the rebuild trigger, apply the rebuild's side effects, swap.
+  psim_status finish_drift() {
+    Real4<R>* nxt = pos[cur ^ 1];
+    if (world > 1) {
+      top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_part, top2_count, top2_rank + 2 * rank, ctrl, parity, c);
+      ++launches;
+      PSIM_NCCL(g_nccl.GroupStart());
+      PSIM_NCCL(g_nccl.AllGather(nxt + shard * rank, nxt, (size_t)shard * 4, NcclType<R>::v, comm, stream));
+      PSIM_NCCL(g_nccl.AllGather(top2_rank + 2 * rank, top2_rank, 2, NcclType<R>::v, comm, stream));
+      PSIM_NCCL(g_nccl.GroupEnd());
+      top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_rank, world, nullptr, ctrl, parity, c);
+      ++launches;
+    } else if (c.slices > 1) {
+      slice_trigger_kernel<R><<<c.slices, 256, 0, stream>>>(nxt, disp, n, ctrl, parity, c);
+      ++launches;
+    } else {
+      top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_part, top2_count, nullptr, ctrl, parity, c);
+      ++launches;
+    }
+    rebuild_effects_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nxt, disp, n, i_lo, i_hi, ctrl, parity, c);
+    ++launches;
+    parity ^= 1;
+    cur ^= 1;
+    cells.invalidate();
+    return PSIM_OK;
+  }
+
+  psim_status advance(int64_t nsteps) override {
+    PSIM_CK(cudaSetDevice(device));
+    if (nsteps < 0) return PSIM_ERR_INVALID_ARGUMENT;
+    const bool can_fuse = fused && algo == PSIM_FORCE_ALL_PAIRS;
+    for (int64_t s = 0; s < nsteps; ++s) {
+      if (!pending_drift) {
+        if (i_hi > i_lo) {
+          const int64_t grid = blocks(i_hi - i_lo, TS);
+          drift_kernel<R, TS><<<grid, TS, 0, stream>>>(pos[cur], pos[cur ^ 1], vel, f_old, f_new, disp, top2_part,
+                                                       i_lo, i_hi, c);
+          top2_count = grid; ++launches;
+        } else top2_count = 0;
+      }
+      pending_drift = false;
+      psim_status st = finish_drift();
+      if (st != PSIM_OK) return st;
+      const bool last = (s == nsteps - 1);
+      if (can_fuse) {
+        st = launch_force(last ? MODE_FORCE_KICK : MODE_FORCE_KICK_DRIFT);
+        if (st != PSIM_OK) return st;
+        pending_drift = !last && (i_hi > i_lo);
+        if (!last && i_hi <= i_lo) top2_count = 0;
+      } else {
+        st = launch_force(MODE_FORCE);
+        if (st != PSIM_OK) return st;
+        if (i_hi > i_lo) {
+          kick_kernel<R, TS><<<blocks(i_hi - i_lo, TS), TS, 0, stream>>>(pos[cur], vel, f_old, f_new, i_lo, i_hi, c);
+          ++launches;
+        }
+      }
+      ++steps;
+    }
+    PSIM_CK(cudaGetLastError());
+    return PSIM_OK;
+  }
+
+  psim_status advance_timed(int64_t nsteps, double* ms) override {
+    PSIM_CK(cudaSetDevice(device));
+    cudaEvent_t a, b;
+    PSIM_CK(cudaEventCreate(&a)); PSIM_CK(cudaEventCreate(&b));
+    PSIM_CK(cudaStreamSynchronize(stream));
+    PSIM_CK(cudaEventRecord(a, stream));
+    psim_status st = advance(nsteps);
+    if (st != PSIM_OK) return st;
+    PSIM_CK(cudaEventRecord(b, stream));
+    PSIM_CK(cudaEventSynchronize(b));
+    float f = 0;
+    PSIM_CK(cudaEventElapsedTime(&f, a, b));
+    if (ms) *ms = f;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    return PSIM_OK;
+  }
+
+  psim_status synchronize() override {
+    PSIM_CK(cudaSetDevice(device));
+    PSIM_CK(cudaStreamSynchronize(stream));
+    PSIM_CK(cudaStreamSynchronize(side));
+    return PSIM_OK;
+  }
+
+  psim_status fetch3(void* host, const Real4<R>* src, int64_t lo, int64_t hi) {
+    if (!host || hi <= lo) return PSIM_OK;
+    pack3_kernel<R, TS><<<blocks(hi - lo, TS), TS, 0, stream>>>(tmp3, src, lo, hi); ++launches;
+    PSIM_CK(cudaMemcpyAsync((R*)host + 3 * lo, tmp3 + 3 * lo, sizeof(R) * 3 * (hi - lo), cudaMemcpyDeviceToHost, stream));
+    PSIM_CK(cudaStreamSynchronize(stream));
+    return PSIM_OK;
+  }
+
+  psim_status get_frame(int32_t* id, void* pos_h, void* vel_h, uint8_t* active_h) override {
+    PSIM_CK(cudaSetDevice(device));
+    if (id) std::memcpy(id, ids.data(), sizeof(int32_t) * n);
+    psim_status st = fetch3(pos_h, pos[cur], 0, n);
+    if (st != PSIM_OK) return st;
+    st = fetch3(vel_h, vel, i_lo, i_hi);
+    if (st != PSIM_OK) return st;
+    if (active_h) {
+      pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(tmp_active, pos[cur], n, c, ctrl); ++launches;
+      PSIM_CK(cudaMemcpyAsync(active_h, tmp_active, (size_t)n, cudaMemcpyDeviceToHost, stream));
+      PSIM_CK(cudaStreamSynchronize(stream));
+    }
+    return PSIM_OK;
+  }
+
+  psim_status get_aux(void* d, void* fo, void* fn) override {
+    PSIM_CK(cudaSetDevice(device));
+    psim_status st;
+    if ((st = fetch3(d, disp, i_lo, i_hi)) != PSIM_OK) return st;
+    if ((st = fetch3(fo, f_old, i_lo, i_hi)) != PSIM_OK) return st;
+    if ((st = fetch3(fn, f_new, i_lo, i_hi)) != PSIM_OK) return st;
+    return PSIM_OK;
+  }
+
+  psim_status get_counters(psim_counters* out) override {
+    PSIM_CK(cudaSetDevice(device));
+    if (!out) return PSIM_ERR_INVALID_ARGUMENT;
+    psim_status st = drain_events();
+    if (st != PSIM_OK) return st;
+    PSIM_CK(cudaMemsetAsync(&ctrl->n_active, 0, sizeof(unsigned long long), stream));
+    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nullptr, pos[cur], n, c, ctrl); ++launches;
+    Control h;
+    PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
+    PSIM_CK(cudaStreamSynchronize(stream));
+    out->steps = steps;
+    out->rebuilds = (int64_t)h.rebuilds;
+    out->kernel_launches = launches + cells.launches;
+    out->force_launches = force_launches;
+    out->force_ms = force_ms;
+    out->force_timed = force_timed;
+    out->n_active = (int64_t)h.n_active;
+    return PSIM_OK;
+  }
+
+  psim_status set_option(int opt, int64_t value) override {
+    switch (opt) {
+      case PSIM_OPT_FORCE_ALGO:
+        if (value != PSIM_FORCE_ALL_PAIRS && value != PSIM_FORCE_CELL_BINNED) return PSIM_ERR_INVALID_ARGUMENT;
+        if (value == PSIM_FORCE_CELL_BINNED && world > 1) {
+          g_last_error = "cell-binned force is single-GPU in this version";
+          return PSIM_ERR_UNSUPPORTED;
+        }
+        algo = (int)value; return PSIM_OK;
+      case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
+      case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
+      case PSIM_OPT_EXACT_DIFF_FILTER: exact_diff = value != 0; return PSIM_OK;
+      default: return PSIM_ERR_INVALID_ARGUMENT;
+    }
+  }
+
+  psim_status ensure_slot(Slot& s) {
+    if (s.d_pos) return PSIM_OK;
+    PSIM_CK(cudaMalloc(&s.d_pos, sizeof(R) * 3 * n)); PSIM_CK(cudaMalloc(&s.d_vel, sizeof(R) * 3 * n));
+    PSIM_CK(cudaMalloc(&s.d_act, (size_t)n));
+    PSIM_CK(cudaMallocHost(&s.h_pos, sizeof(R) * 3 * n)); PSIM_CK(cudaMallocHost(&s.h_vel, sizeof(R) * 3 * n));
+    PSIM_CK(cudaMallocHost(&s.h_act, (size_t)n));
+    PSIM_CK(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+    PSIM_CK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    return PSIM_OK;
+  }
+
+  // Pack the post-kick state into the slot's device staging on the stepping
+  // stream (cheap, O(N)), then drain it to pinned memory on the side stream so
+  // the time loop never waits for PCIe.
+  psim_status snapshot_async(int slot) override {
+    PSIM_CK(cudaSetDevice(device));
+    if (slot < 0 || slot >= PSIM_FRAME_SLOTS) return PSIM_ERR_INVALID_ARGUMENT;
+    Slot& s = slots[slot];
+    psim_status st = ensure_slot(s);
+    if (st != PSIM_OK) return st;
+    if (s.used) PSIM_CK(cudaStreamWaitEvent(stream, s.done, 0));   // previous drain of this slot
+    // while a fused kernel has already drifted, pos[cur] still holds x_n
+    pack3_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_pos, pos[cur], 0, n);
+    if (i_hi > i_lo) pack3_kernel<R, TS><<<blocks(i_hi - i_lo, TS), TS, 0, stream>>>(s.d_vel, vel, i_lo, i_hi);
+    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_act, pos[cur], n, c, ctrl);
+    launches += 3;
+    PSIM_CK(cudaEventRecord(s.ready, stream));
+    PSIM_CK(cudaStreamWaitEvent(side, s.ready, 0));
+    PSIM_CK(cudaMemcpyAsync(s.h_pos, s.d_pos, sizeof(R) * 3 * n, cudaMemcpyDeviceToHost, side));
+    if (i_hi > i_lo)
+      PSIM_CK(cudaMemcpyAsync(s.h_vel + 3 * i_lo, s.d_vel + 3 * i_lo, sizeof(R) * 3 * (i_hi - i_lo),
+                              cudaMemcpyDeviceToHost, side));
+    PSIM_CK(cudaMemcpyAsync(s.h_act, s.d_act, (size_t)n, cudaMemcpyDeviceToHost, side));
+    PSIM_CK(cudaEventRecord(s.done, side));
+    s.used = true;
+    return PSIM_OK;
+  }
+
+  psim_status snapshot_wait(int slot, const int32_t** id, const void** pos_h, const void** vel_h,
+                            const uint8_t** active_h) override {
+    PSIM_CK(cudaSetDevice(device));
+    if (slot < 0 || slot >= PSIM_FRAME_SLOTS || !slots[slot].used) return PSIM_ERR_INVALID_ARGUMENT;
+    Slot& s = slots[slot];
+    PSIM_CK(cudaEventSynchronize(s.done));
+    if (id) *id = ids.data();
+    if (pos_h) *pos_h = s.h_pos;
+    if (vel_h) *vel_h = s.h_vel;
+    if (active_h) *active_h = s.h_act;
+    return PSIM_OK;
+  }
+
+  psim_status count_pairs(int64_t* pairs) override {
+    PSIM_CK(cudaSetDevice(device));
+    unsigned long long* d = nullptr;
+    PSIM_CK(cudaMalloc(&d, sizeof *d));
+    PSIM_CK(cudaMemsetAsync(d, 0, sizeof *d, stream));
+    if (i_hi > i_lo) {
+      count_pairs_kernel<R, 128><<<blocks(i_hi - i_lo, 128), 128, 0, stream>>>(pos[cur], n_pad, i_lo, i_hi, c, d);
+      ++launches;
+    }
+    unsigned long long h = 0;
+    PSIM_CK(cudaMemcpyAsync(&h, d, sizeof h, cudaMemcpyDeviceToHost, stream));
+    PSIM_CK(cudaStreamSynchronize(stream));
+    cudaFree(d);
+    if (pairs) *pairs = (int64_t)h;
+    return PSIM_OK;
+  }
+
+  psim_status energy(double* k, double* u, double* mom) override {
+    PSIM_CK(cudaSetDevice(device));
+    double* d = nullptr;
+    PSIM_CK(cudaMalloc(&d, 5 * sizeof(double)));
+    PSIM_CK(cudaMemsetAsync(d, 0, 5 * sizeof(double), stream));
+    if (i_hi > i_lo) {
+      energy_kernel<R, 128><<<blocks(i_hi - i_lo, 128), 128, 0, stream>>>(pos[cur], vel, n_pad, i_lo, i_hi, c, mass, d);
+      ++launches;
+    }
+    double h[5];
+    PSIM_CK(cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, stream));
+    PSIM_CK(cudaStreamSynchronize(stream));
+    cudaFree(d);
+    if (k) *k = h[0];
+    if (u) *u = h[1];
+    if (mom) { mom[0] = h[2]; mom[1] = h[3]; mom[2] = h[4]; }
+    return PSIM_OK;
+  }
+
+  psim_status get_shard(int64_t* lo, int64_t* hi) override {
+    if (lo) *lo = i_lo;
+    if (hi) *hi = i_hi;
+    return PSIM_OK;
+  }
+};
+
+template <class R>
+static psim_status create_t(const psim_params* p, int64_t n, const int32_t* id, const void* pos, const void* vel,
+                            const uint8_t* active, int device, int rank, int world, const void* uid,
+                            psim_sim** out) {
+  SimT<R>* s = new SimT<R>();
+  psim_status st = s->init(*p, n, id, pos, vel, active, device, rank, world, uid);
+  if (st != PSIM_OK) { delete s; return st; }
+  *out = s;
+  return PSIM_OK;
+}
+
+static psim_status create_any(const psim_params* p, int precision, int64_t n, const int32_t* id, const void* pos,
+                              const void* vel, const uint8_t* active, int device, int rank, int world,
+                              const void* uid, psim_sim** out) {
+  if (!p || !out || !pos) return PSIM_ERR_INVALID_ARGUMENT;
+  if (precision != 4 && precision != 8) return PSIM_ERR_INVALID_ARGUMENT;
+  if (n <= 0) return PSIM_ERR_NO_PARTICLES;
+  if (world < 1 || rank < 0 || rank >= world) return PSIM_ERR_INVALID_ARGUMENT;
+  if (world > 1 && !uid) return PSIM_ERR_INVALID_ARGUMENT;
+  *out = nullptr;
+  std::vector<int32_t> seq;
+  if (!id) { seq.resize(n); for (int64_t i = 0; i < n; ++i) seq[i] = (int32_t)(i + 1); id = seq.data(); }
+  if (precision == 4) return create_t<float>(p, n, id, pos, vel, active, device, rank, world, uid, out);
+  return create_t<double>(p, n, id, pos, vel, active, device, rank, world, uid, out);
+}
+
+template <class R>
+static psim_status fma_peak_t(int device, double* tflops, double* sm_mhz) {
+  PSIM_CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  PSIM_CK(cudaGetDeviceProperties(&prop, device));
+  constexpr int ILP = 8;
+  const int grid = prop.multiProcessorCount * 8, block = 256, iters = 4096;
+  R* out = nullptr; long long* cyc = nullptr;
+  PSIM_CK(cudaMalloc(&out, sizeof(R) * (size_t)grid * block));
+  PSIM_CK(cudaMalloc(&cyc, sizeof(long long) * grid));
+  cudaEvent_t a, b;
+  PSIM_CK(cudaEventCreate(&a)); PSIM_CK(cudaEventCreate(&b));
+  double best = 0, best_mhz = 0;
+  for (int rep = 0; rep < 8; ++rep) {
+    PSIM_CK(cudaEventRecord(a, 0));
+    fma_peak_kernel<R, ILP><<<grid, block>>>(out, iters, (R)1.0000001, (R)1e-7, cyc);
+    PSIM_CK(cudaEventRecord(b, 0));
+    PSIM_CK(cudaEventSynchronize(b));
+    float ms = 0;
+    PSIM_CK(cudaEventElapsedTime(&ms, a, b));
+    const double flops = 2.0 * ILP * (double)iters * grid * block;
+    const double tf = flops / (ms * 1e-3) / 1e12;
+    if (rep >= 2 && tf > best) {
+      best = tf;
+      // each SM runs 8 blocks of this grid concurrently -> per-block cycle count ~ kernel duration
+      long long h = 0;
+      PSIM_CK(cudaMemcpy(&h, cyc, sizeof h, cudaMemcpyDeviceToHost));
+      best_mhz = (double)h / (ms * 1e-3) / 1e6;
+    }
+  }
+  cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out); cudaFree(cyc);
+  PSIM_CK(cudaGetLastError());
+  if (tflops) *tflops = best;
+  if (sm_mhz) *sm_mhz = best_mhz;
+  return PSIM_OK;
+}
+
+}  // namespace psim
+
+// ------------------------------ extern "C" --------------------------------
+extern "C" {
+
+psim_status psim_create(const psim_params* params, int precision, int64_t n, const int32_t* id, const void* pos,
+                        const void* vel, int device, psim_sim** out) {
+  return create_any(params, precision, n, id, pos, vel, nullptr, device, 0, 1, nullptr, out);
+}
+
+psim_status psim_create_sharded(const psim_params* params, int precision, int64_t n, const int32_t* id,
+                                const void* pos, const void* vel, int device, int rank, int world,
+                                const void* nccl_unique_id, psim_sim** out) {
+  return create_any(params, precision, n, id, pos, vel, nullptr, device, rank, world, nccl_unique_id, out);
+}
+
+psim_status psim_comm_unique_id(void* out128) {
+  if (!out128) return PSIM_ERR_INVALID_ARGUMENT;
+  if (!g_nccl.load()) return PSIM_ERR_COMM;
+  ncclUniqueId id;
+  PSIM_NCCL(g_nccl.GetUniqueId(&id));
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  std::memcpy(out128, &id, 128);
+  return PSIM_OK;
+}
+
+psim_status psim_destroy(psim_sim* sim) { delete sim; return PSIM_OK; }
+
+#define PSIM_FWD(sim, expr) ((sim) ? (sim)->expr : PSIM_ERR_INVALID_ARGUMENT)
+
+psim_status psim_set_option(psim_sim* sim, int option, int64_t value) { return PSIM_FWD(sim, set_option(option, value)); }
+psim_status psim_advance(psim_sim* sim, int64_t nsteps) { return PSIM_FWD(sim, advance(nsteps)); }
+psim_status psim_synchronize(psim_sim* sim) { return PSIM_FWD(sim, synchronize()); }
+psim_status psim_advance_timed(psim_sim* sim, int64_t nsteps, double* ms) { return PSIM_FWD(sim, advance_timed(nsteps, ms)); }
+psim_status psim_get_frame(psim_sim* sim, int32_t* id, void* pos, void* vel, uint8_t* active) {
+  return PSIM_FWD(sim, get_frame(id, pos, vel, active));
+}
+psim_status psim_get_aux(psim_sim* sim, void* d, void* fo, void* fn) { return PSIM_FWD(sim, get_aux(d, fo, fn)); }
+psim_status psim_get_counters(psim_sim* sim, psim_counters* out) { return PSIM_FWD(sim, get_counters(out)); }
+psim_status psim_get_shard(psim_sim* sim, int64_t* lo, int64_t* hi) { return PSIM_FWD(sim, get_shard(lo, hi)); }
+psim_status psim_set_positions(psim_sim* sim, const void* pos, const uint8_t* active) {
+  return PSIM_FWD(sim, set_positions(pos, active));
+}
+psim_status psim_snapshot_async(psim_sim* sim, int slot) { return PSIM_FWD(sim, snapshot_async(slot)); }
+psim_status psim_snapshot_wait(psim_sim* sim, int slot, const int32_t** id, const void** pos, const void** vel,
+                               const uint8_t** active) {
+  return PSIM_FWD(sim, snapshot_wait(slot, id, pos, vel, active));
+}
+psim_status psim_count_pairs_in_range(psim_sim* sim, int64_t* pairs) { return PSIM_FWD(sim, count_pairs(pairs)); }
+psim_status psim_energy(psim_sim* sim, double* k, double* u, double mom[3]) { return PSIM_FWD(sim, energy(k, u, mom)); }
+
+psim_status psim_compute_forces_host(const psim_params* params, int precision, int64_t n, const void* pos,
+                                     const uint8_t* active, int algo, int device, void* force,
+                                     int64_t* pairs_in_range) {
+  if (!force) return PSIM_ERR_INVALID_ARGUMENT;
+  psim_sim* s = nullptr;
+  std::vector<uint8_t> all;
+  if (!active) { all.assign((size_t)std::max<int64_t>(n, 0), 1); active = all.data(); }
+  psim_status st = create_any(params, precision, n, nullptr, pos, nullptr, active, device, 0, 1, nullptr, &s);
+  if (st != PSIM_OK) return st;
+  if (algo != PSIM_FORCE_ALL_PAIRS) {
+    st = s->set_option(PSIM_OPT_FORCE_ALGO, algo);
+    if (st == PSIM_OK) st = s->set_positions(pos, active);
+  }
+  if (st == PSIM_OK) st = s->get_aux(nullptr, nullptr, force);
+  if (st == PSIM_OK && pairs_in_range) st = s->count_pairs(pairs_in_range);
+  delete s;
+  return st;
+}
+
+psim_status psim_measure_fma_peak(int precision, int device, double* tflops, double* sm_mhz) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return PSIM_ERR_NO_DEVICE; }
+  if (device < 0) device = 0;
+  if (precision == 4) return fma_peak_t<float>(device, tflops, sm_mhz);
+  if (precision == 8) return fma_peak_t<double>(device, tflops, sm_mhz);
+  return PSIM_ERR_INVALID_ARGUMENT;
+}
+
+const char* psim_status_string(int status) {
+  switch (status) {
+    case PSIM_OK: return "ok";
+    case PSIM_ERR_INVALID_ARGUMENT: return "invalid argument";
+    case PSIM_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+    case PSIM_ERR_CUDA: return "CUDA error";
+    case PSIM_ERR_NO_PARTICLES: return "No particles in particle file";
+    case PSIM_ERR_UNSUPPORTED: return "unsupported configuration";
+    case PSIM_ERR_COMM: return "communicator (NCCL) error";
+    case PSIM_ERR_IO: return "I/O error";
+    default: return "unknown status";
+  }
+}
+
+const char* psim_last_error(void) { return g_last_error.c_str(); }
+const char* psim_version(void) { return "particle_simulation_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

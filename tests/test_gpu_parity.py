@@ -1,0 +1,114 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI
+(particle_simulation_b200.native -> libpsim_b200.so), against the CPU oracle on
+the same seeded inputs.
+
+Tolerances.  A pair's contribution is computed with the same
+correctly rounded operations on both sides, so one force evaluation differs by
+summation order only:
+  f64: |f_gpu - f_oracle| <= 1e-12 * max|f|   f32: <= 1e-5 * max|f|
+Trajectories are chaotic; K-step comparisons use short horizons and
+  f64: 1e-9 absolute on positions,  f32: 2e-4.
+"""
+import numpy as np
+import pytest
+
+from conftest import two_cubes
+
+pytestmark = pytest.mark.gpu
+
+FTOL = {4: 1e-5, 8: 1e-12}
+XTOL = {4: 2e-4, 8: 1e-9}
+
+
+def _ref_files():
+    import os
+    from conftest import GOLDEN
+    return os.path.join(GOLDEN, "two_cubes_432.dat")
+
+
+@pytest.mark.parametrize("precision", [4, 8])
+@pytest.mark.parametrize("exact_diff", [0, 1])
+def test_initial_forces_match_oracle(psim, oracle, precision, exact_diff):
+    ids, pos, vel = two_cubes()
+    p = psim.make_params()
+    op = oracle.make_params()
+    o = oracle.Oracle(op, precision, ids, pos, vel)
+    _, _, f_ref = o.aux()
+    sim = psim.Simulation(p, ids, pos, vel, precision)
+    if exact_diff:
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 1)
+        sim.set_positions(pos)
+    f = sim.forces()
+    scale = np.abs(f_ref).max()
+    assert scale > 0
+    assert np.abs(f - f_ref).max() <= FTOL[precision] * scale
+    # and against the independent brute-force double evaluation
+    bf, pairs = oracle.bruteforce(op, precision, pos)
+    assert np.abs(f - bf).max() <= 4 * FTOL[precision] * scale
+    assert sim.pairs_in_range() == pairs
+    sim.close()
+
+
+@pytest.mark.parametrize("precision", [4, 8])
+@pytest.mark.parametrize("fused", [0, 1])
+def test_k_steps_match_oracle(psim, oracle, precision, fused):
+    ids, pos, vel = two_cubes()
+    p = psim.make_params()
+    o = oracle.Oracle(oracle.make_params(), precision, ids, pos, vel)
+    sim = psim.Simulation(p, ids, pos, vel, precision)
+    sim.set_option(psim.OPT_FUSED_STEP, fused)
+    K = 60
+    for chunk in (1, 2, K - 3):
+        o.advance(chunk)
+        sim.advance(chunk)
+    _, x_ref, v_ref, a_ref = o.frame()
+    _, x, v, a = sim.frame()
+    d_ref, fo_ref, fn_ref = o.aux()
+    d, fo, fn = sim.aux()
+    assert np.array_equal(a, a_ref)
+    assert np.abs(x - x_ref).max() <= XTOL[precision]
+    assert np.abs(v - v_ref).max() <= XTOL[precision] * 100
+    fs = np.abs(fn_ref).max()
+    assert np.abs(fn - fn_ref).max() <= 1e3 * FTOL[precision] * fs
+    assert np.abs(fo - fo_ref).max() <= 1e3 * FTOL[precision] * fs
+    assert np.abs(d - d_ref).max() <= XTOL[precision]
+    c = sim.counters()
+    assert c.steps == K and c.rebuilds == o.rebuilds
+    sim.close()
+
+
+@pytest.mark.parametrize("precision", [4, 8])
+def test_particles_leaving_the_box_are_deactivated_like_the_reference(psim, oracle, precision):
+    # a small box: the fast cube leaves it during the run
+    ids, pos, vel = two_cubes(side=4, speed=40.0, origin=3.0)
+    kw = dict(length_of_area=(30.0, 30.0, 30.0), delta_t=0.002)
+    o = oracle.Oracle(oracle.make_params(**kw), precision, ids, pos, vel)
+    sim = psim.Simulation(psim.make_params(**kw), ids, pos, vel, precision)
+    total = 0
+    for _ in range(12):
+        o.advance(25)
+        sim.advance(25)
+        total += 25
+        _, x_ref, v_ref, a_ref = o.frame()
+        _, x, v, a = sim.frame()
+        assert np.array_equal(a, a_ref), "active flags differ after %d steps" % total
+        assert sim.counters().rebuilds == o.rebuilds
+        keep = a_ref.astype(bool)
+        if keep.any():
+            assert np.abs(x[keep] - x_ref[keep]).max() <= 50 * XTOL[precision]
+    assert (a_ref == 0).any(), "test is vacuous: nothing left the box"
+    sim.close()
+
+
+def test_conservation_and_energy(psim, oracle):
+    ids, pos, vel = two_cubes()
+    sim = psim.Simulation(psim.make_params(), ids, pos, vel, 8)
+    k0, u0, p0 = sim.energy()
+    o = oracle.Oracle(oracle.make_params(), 8, ids, pos, vel)
+    ko, uo, po = o.energy()
+    assert abs(k0 - ko) <= 1e-9 * abs(ko) and abs(u0 - uo) <= 1e-9 * abs(uo)
+    sim.advance(400)
+    k1, u1, p1 = sim.energy()
+    assert np.abs(p1 - p0).max() <= 1e-9 * np.abs(p0).max()          # momentum: pairwise antisymmetric forces
+    assert abs((k1 + u1) - (k0 + u0)) <= 2e-5 * abs(k0 + u0)          # velocity Verlet, dt = 1e-3
+    sim.close()
