@@ -193,6 +193,38 @@ psim_status psim_count_pairs_in_range(psim_sim* sim, int64_t* pairs);
 psim_status psim_energy(psim_sim* sim, double* kinetic, double* potential,
                         double momentum[3]);
 
+/* --- for callers that cannot allocate device memory ----------------------- */
+
+/* No counterpart in the reference (there, every array is ordinary host
+ * memory).  This is the drift step, compute_locations, offered to hosts that
+ * will not let a library allocate on the GPU: a driver that has committed the
+ * device to its own memory plan (OpenACC / CUDA Fortran arrays already
+ * resident, a fixed per-process memory budget), or a stepping loop that cannot
+ * afford the device-wide synchronisation of cudaMalloc / cudaFree.  It works in
+ * place on packed xyz DEVICE arrays the caller owns — pos, force_old,
+ * force_new, displacement are updated, vel and active (may be NULL = all
+ * active) are read — and writes the rebuild verdict
+ * (dr_max_first + dr_max_second > dr_max_tolerable) as 0/1 to the device int
+ * *rebuild_flag_dev.  Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the
+ * default stream); the CUDA device that is current at the call is used.
+ *
+ * Its reduction scratch is a fixed array inside the library image, not an
+ * allocation: PSIM_STATIC_SCRATCH_BYTES per GPU that loads the library, held
+ * until the process exits.  Consequences: n may not exceed
+ * PSIM_STATIC_MAX_PARTICLES (PSIM_ERR_INVALID_ARGUMENT otherwise, nothing is
+ * launched); all calls on a GPU share the array, so calls that may overlap on
+ * the GPU (different streams or host threads) race and must be ordered by the
+ * caller; the first call on each device resolves the array's device address
+ * and should be made during set-up, before any stream capture begins.  Calls
+ * no cudaMalloc, cudaFree or any other allocating routine. */
+#define PSIM_STATIC_MAX_PARTICLES 1048576
+#define PSIM_STATIC_SCRATCH_BYTES 65792
+psim_status psim_compute_locations_static(const psim_params* params, int precision, int64_t n,
+                                          void* pos_dev, const void* vel_dev,
+                                          void* force_old_dev, void* force_new_dev,
+                                          void* displacement_dev, const uint8_t* active_dev,
+                                          int32_t* rebuild_flag_dev, void* cuda_stream);
+
 /* --- measurement helpers ------------------------------------------------- */
 
 /* Dependent-free FMA loop on every SM: the measured FMA-pipe peak of this GPU

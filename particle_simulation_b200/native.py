@@ -82,7 +82,7 @@ EXPORTS = (
     "psim_advance", "psim_synchronize", "psim_advance_timed", "psim_get_frame", "psim_get_aux",
     "psim_get_counters", "psim_get_shard", "psim_set_positions", "psim_snapshot_async", "psim_snapshot_wait",
     "psim_compute_forces_host", "psim_count_pairs_in_range", "psim_energy", "psim_measure_fma_peak",
-    "psim_status_string", "psim_last_error", "psim_version",
+    "psim_status_string", "psim_last_error", "psim_version", "psim_compute_locations_static",
 )
 
 
@@ -123,6 +123,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         "psim_count_pairs_in_range": [vp, C.POINTER(i64)],
         "psim_energy": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "psim_measure_fma_peak": [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)],
+        "psim_compute_locations_static": [PP, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)
@@ -308,6 +309,21 @@ def compute_forces(params: Params, pos, precision: int = 4, active=None, algo: i
     _check(lib.psim_compute_forces_host(C.byref(params), precision, n, _ptr(pos), _ptr(active), algo, device,
                                         _ptr(out), C.byref(pairs)), "psim_compute_forces_host")
     return out, pairs.value
+
+
+STATIC_MAX_PARTICLES = 1048576
+
+
+def compute_locations_static(params: Params, precision: int, n: int, pos_dev: int, vel_dev: int, force_old_dev: int,
+                             force_new_dev: int, displacement_dev: int, active_dev: int | None,
+                             rebuild_flag_dev: int, cuda_stream: int | None = None):
+    """psim_compute_locations_static: one drift step, in place, on device arrays
+    the caller owns (raw device addresses), for hosts that cannot let the
+    library allocate GPU memory.  Limited to STATIC_MAX_PARTICLES; calls that
+    can overlap on one GPU must be ordered by the caller (shared fixed scratch)."""
+    _check(load().psim_compute_locations_static(C.byref(params), precision, n, pos_dev, vel_dev, force_old_dev,
+                                                force_new_dev, displacement_dev, active_dev, rebuild_flag_dev,
+                                                cuda_stream), "psim_compute_locations_static")
 
 
 def comm_unique_id() -> bytes:
