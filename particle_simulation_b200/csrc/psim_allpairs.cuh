@@ -71,6 +71,36 @@ __device__ __forceinline__ void block_top2_store(R first, R second, R* part) {
   }
 }
 
+// What follows the force sum of one owned particle, shared by every force
+// kernel: MODE 0 stores the force; MODE 1 also kicks (stoermer:200-201); MODE 2
+// also performs the NEXT step's drift (stoermer:155-165) into the other
+// position buffer and feeds |displacement| to the block's top-2.
+template <class R, int MODE>
+__device__ __forceinline__ void step_epilogue(const StepArgs<R>& a, int64_t i, R fx, R fy, R fz,
+                                              R& first, R& second) {
+  const Consts<R>& c = a.c;
+  const Real4<R> p = a.pos_cur[i];
+  if (p.w >= c.huge) {                       // inactive: carried along untouched
+    if (MODE == MODE_FORCE_KICK_DRIFT) a.pos_nxt[i] = p;
+    return;
+  }
+  Real4<R> fn; fn.x = fx; fn.y = fy; fn.z = fz; fn.w = (R)0;
+  if (MODE == MODE_FORCE) { a.f_new[i] = fn; return; }
+  Real4<R> v = a.vel[i];
+  const Real4<R> fo = a.f_old[i];
+  v.x = r_add(v.x, r_mul(c.tmf, r_add(fn.x, fo.x)));
+  v.y = r_add(v.y, r_mul(c.tmf, r_add(fn.y, fo.y)));
+  v.z = r_add(v.z, r_mul(c.tmf, r_add(fn.z, fo.z)));
+  a.vel[i] = v;
+  if (MODE == MODE_FORCE_KICK) { a.f_new[i] = fn; return; }
+  a.f_old[i] = fn;                           // force_old <- force_new
+  Real4<R> d = a.disp[i], xn;
+  const R dr = drift_one(c, p, v, fn.x, fn.y, fn.z, d, xn);
+  a.disp[i] = d;
+  a.pos_nxt[i] = xn;
+  top2_push(first, second, dr);
+}
+
 // T threads, RI i-particles per thread (register tile), j-tiles of T records
 // double-buffered in shared memory, U j's per filter group.
 template <class R, int T, int RI, int MODE, bool EXACT_DIFF>
@@ -164,33 +194,8 @@ allpairs_step_kernel(const StepArgs<R> a) {
   // --- epilogue: store the force; kick; drift into the other position buffer ---
   R first = (R)0, second = (R)0;
 #pragma unroll
-  for (int r = 0; r < RI; ++r) {
-    const int64_t i = ig[r];
-    if (i < 0) continue;
-    const Real4<R> p = a.pos_cur[i];
-    const bool active = !(p.w >= c.huge);
-    if (!active) {
-      if (MODE == MODE_FORCE_KICK_DRIFT) a.pos_nxt[i] = p;
-      continue;
-    }
-    Real4<R> fn; fn.x = fx[r]; fn.y = fy[r]; fn.z = fz[r]; fn.w = (R)0;
-    if (MODE == MODE_FORCE) { a.f_new[i] = fn; continue; }
-    // kick (stoermer:200-201)
-    Real4<R> v = a.vel[i];
-    const Real4<R> fo = a.f_old[i];
-    v.x = r_add(v.x, r_mul(c.tmf, r_add(fn.x, fo.x)));
-    v.y = r_add(v.y, r_mul(c.tmf, r_add(fn.y, fo.y)));
-    v.z = r_add(v.z, r_mul(c.tmf, r_add(fn.z, fo.z)));
-    a.vel[i] = v;
-    if (MODE == MODE_FORCE_KICK) { a.f_new[i] = fn; continue; }
-    // drift of the next step (stoermer:155-165): force_old <- force_new
-    a.f_old[i] = fn;
-    Real4<R> d = a.disp[i], xn;
-    const R dr = drift_one(c, p, v, fn.x, fn.y, fn.z, d, xn);
-    a.disp[i] = d;
-    a.pos_nxt[i] = xn;
-    top2_push(first, second, dr);
-  }
+  for (int r = 0; r < RI; ++r)
+    if (ig[r] >= 0) step_epilogue<R, MODE>(a, ig[r], fx[r], fy[r], fz[r], first, second);
   if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part);
 }
 

@@ -263,7 +263,8 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMemcpyAsync(tmp3, pos_h, sizeof(R) * 3 * n, cudaMemcpyHostToDevice, stream));
     if (active_h) PSIM_CK(cudaMemcpyAsync(tmp_active, active_h, (size_t)n, cudaMemcpyHostToDevice, stream));
     init_positions_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(pos[0], pos[1], tmp3,
-                                                                     active_h ? tmp_active : nullptr, n, n_pad, c);
+                                                                     active_h ? tmp_active : nullptr,
+                                                                     cells.orig_or_null(), n, n_pad, c);
     unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(disp, nullptr, n, n_pad);
     unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(f_old, nullptr, n, n_pad);
     unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(f_new, nullptr, n, n_pad);
@@ -348,7 +349,7 @@ class SimT final : public psim_sim {
       top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_rank, world, nullptr, ctrl, parity, c);
       ++launches;
     } else if (c.slices > 1) {
-      slice_trigger_kernel<R><<<c.slices, 256, 0, stream>>>(nxt, disp, n, ctrl, parity, c);
+      slice_trigger_kernel<R><<<c.slices, 256, 0, stream>>>(nxt, disp, cells.orig_or_null(), n, ctrl, parity, c);
       ++launches;
     } else {
       top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_part, top2_count, nullptr, ctrl, parity, c);
@@ -356,16 +357,17 @@ class SimT final : public psim_sim {
     }
     rebuild_effects_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nxt, disp, n, i_lo, i_hi, ctrl, parity, c);
     ++launches;
+    // cell path: re-order the state by cell when (and only when) the trigger fired
+    if (algo == PSIM_FORCE_CELL_BINNED && cells.allocated()) cells.rebin(*this, nxt, parity, false);
     parity ^= 1;
     cur ^= 1;
-    cells.invalidate();
     return PSIM_OK;
   }
 
   psim_status advance(int64_t nsteps) override {
     PSIM_CK(cudaSetDevice(device));
     if (nsteps < 0) return PSIM_ERR_INVALID_ARGUMENT;
-    const bool can_fuse = fused && algo == PSIM_FORCE_ALL_PAIRS;
+    const bool can_fuse = fused;
     for (int64_t s = 0; s < nsteps; ++s) {
       if (!pending_drift) {
         if (i_hi > i_lo) {
@@ -424,7 +426,7 @@ class SimT final : public psim_sim {
 
   psim_status fetch3(void* host, const Real4<R>* src, int64_t lo, int64_t hi) {
     if (!host || hi <= lo) return PSIM_OK;
-    pack3_kernel<R, TS><<<blocks(hi - lo, TS), TS, 0, stream>>>(tmp3, src, lo, hi); ++launches;
+    pack3_kernel<R, TS><<<blocks(hi - lo, TS), TS, 0, stream>>>(tmp3, src, cells.orig_or_null(), lo, hi); ++launches;
     PSIM_CK(cudaMemcpyAsync((R*)host + 3 * lo, tmp3 + 3 * lo, sizeof(R) * 3 * (hi - lo), cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     return PSIM_OK;
@@ -438,7 +440,7 @@ class SimT final : public psim_sim {
     st = fetch3(vel_h, vel, i_lo, i_hi);
     if (st != PSIM_OK) return st;
     if (active_h) {
-      pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(tmp_active, pos[cur], n, c, ctrl); ++launches;
+      pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(tmp_active, pos[cur], cells.orig_or_null(), n, c, ctrl); ++launches;
       PSIM_CK(cudaMemcpyAsync(active_h, tmp_active, (size_t)n, cudaMemcpyDeviceToHost, stream));
       PSIM_CK(cudaStreamSynchronize(stream));
     }
@@ -460,7 +462,7 @@ class SimT final : public psim_sim {
     psim_status st = drain_events();
     if (st != PSIM_OK) return st;
     PSIM_CK(cudaMemsetAsync(&ctrl->n_active, 0, sizeof(unsigned long long), stream));
-    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nullptr, pos[cur], n, c, ctrl); ++launches;
+    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nullptr, pos[cur], nullptr, n, c, ctrl); ++launches;
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
@@ -482,7 +484,7 @@ class SimT final : public psim_sim {
           g_last_error = "cell-binned force is single-GPU in this version";
           return PSIM_ERR_UNSUPPORTED;
         }
-        algo = (int)value; return PSIM_OK;
+        algo = (int)value; cells.invalidate(); return PSIM_OK;
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER: exact_diff = value != 0; return PSIM_OK;
@@ -512,9 +514,10 @@ class SimT final : public psim_sim {
     if (st != PSIM_OK) return st;
     if (s.used) PSIM_CK(cudaStreamWaitEvent(stream, s.done, 0));   // previous drain of this slot
     // while a fused kernel has already drifted, pos[cur] still holds x_n
-    pack3_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_pos, pos[cur], 0, n);
-    if (i_hi > i_lo) pack3_kernel<R, TS><<<blocks(i_hi - i_lo, TS), TS, 0, stream>>>(s.d_vel, vel, i_lo, i_hi);
-    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_act, pos[cur], n, c, ctrl);
+    const int32_t* og = cells.orig_or_null();
+    pack3_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_pos, pos[cur], og, 0, n);
+    if (i_hi > i_lo) pack3_kernel<R, TS><<<blocks(i_hi - i_lo, TS), TS, 0, stream>>>(s.d_vel, vel, og, i_lo, i_hi);
+    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_act, pos[cur], og, n, c, ctrl);
     launches += 3;
     PSIM_CK(cudaEventRecord(s.ready, stream));
     PSIM_CK(cudaStreamWaitEvent(side, s.ready, 0));

@@ -96,15 +96,23 @@ top2_merge_kernel(const R* __restrict__ pairs, int64_t count, R* out_pair, Contr
 // step clears it).
 template <class R>
 __global__ void __launch_bounds__(256)
-slice_trigger_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restrict__ disp, int64_t n,
-                     Control* ctrl, int parity, Consts<R> c) {
+slice_trigger_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restrict__ disp,
+                     const int32_t* __restrict__ orig, int64_t n, Control* ctrl, int parity, Consts<R> c) {
   __shared__ R s_first[8], s_second[8];
   const int64_t per = n / c.slices;
   const int64_t lo = per * blockIdx.x;
   const int64_t hi = (blockIdx.x == (unsigned)c.slices - 1) ? n : per * (blockIdx.x + 1);
   R first = (R)0, second = (R)0;
-  for (int64_t i = lo + threadIdx.x; i < hi; i += 256)
-    if (!(pos[i].w >= c.huge)) top2_push(first, second, disp[i].w);
+  if (orig) {
+    // state is cell-ordered: visit every slot, keep those whose particle index is in the slice
+    for (int64_t k = threadIdx.x; k < n; k += 256) {
+      const int64_t i = orig[k];
+      if (i >= lo && i < hi && !(pos[k].w >= c.huge)) top2_push(first, second, disp[k].w);
+    }
+  } else {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += 256)
+      if (!(pos[i].w >= c.huge)) top2_push(first, second, disp[i].w);
+  }
   top2_warp_reduce(first, second);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) { s_first[warp] = first; s_second[warp] = second; }
@@ -149,15 +157,17 @@ rebuild_effects_kernel(Real4<R>* __restrict__ pos, Real4<R>* __restrict__ disp, 
 template <class R, int T>
 __global__ void __launch_bounds__(T)
 init_positions_kernel(Real4<R>* __restrict__ pos_a, Real4<R>* __restrict__ pos_b, const R* __restrict__ xyz,
-                      const unsigned char* __restrict__ active_in, int64_t n, int64_t n_pad, Consts<R> c) {
+                      const unsigned char* __restrict__ active_in, const int32_t* __restrict__ orig,
+                      int64_t n, int64_t n_pad, Consts<R> c) {
   const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
   if (i >= n_pad) return;
   Real4<R> p; p.x = p.y = p.z = (R)0; p.w = c.huge;
   if (i < n) {
-    p.x = xyz[3 * i]; p.y = xyz[3 * i + 1]; p.z = xyz[3 * i + 2];
+    const int64_t o = orig ? orig[i] : i;      // slot i holds particle o
+    p.x = xyz[3 * o]; p.y = xyz[3 * o + 1]; p.z = xyz[3 * o + 2];
     bool ok = !(p.x > c.area[0] || p.y > c.area[1] || p.z > c.area[2] || p.x < (R)0 || p.y < (R)0 || p.z < (R)0);
     ok = ok && inside_grid(p.x, p.y, p.z, c);
-    if (active_in) ok = active_in[i] != 0;     // operator form: the caller decides
+    if (active_in) ok = active_in[o] != 0;     // operator form: the caller decides
     p.w = ok ? filter_weight(p.x, p.y, p.z, c) : c.huge;
   }
   pos_a[i] = p;
@@ -177,22 +187,24 @@ unpack3_kernel(Real4<R>* __restrict__ dst, const R* __restrict__ xyz, int64_t n,
 // Pack a record array into xyz triples (frame output / diagnostics).
 template <class R, int T>
 __global__ void __launch_bounds__(T)
-pack3_kernel(R* __restrict__ xyz, const Real4<R>* __restrict__ src, int64_t lo, int64_t hi) {
+pack3_kernel(R* __restrict__ xyz, const Real4<R>* __restrict__ src, const int32_t* __restrict__ orig,
+             int64_t lo, int64_t hi) {
   const int64_t i = lo + (int64_t)blockIdx.x * T + threadIdx.x;
   if (i >= hi) return;
   const Real4<R> v = src[i];
-  xyz[3 * i] = v.x; xyz[3 * i + 1] = v.y; xyz[3 * i + 2] = v.z;
+  const int64_t o = orig ? orig[i] : i;        // back to array order
+  xyz[3 * o] = v.x; xyz[3 * o + 1] = v.y; xyz[3 * o + 2] = v.z;
 }
 
 template <class R, int T>
 __global__ void __launch_bounds__(T)
-pack_active_kernel(unsigned char* __restrict__ active, const Real4<R>* __restrict__ pos, int64_t n, Consts<R> c,
-                   Control* ctrl) {
+pack_active_kernel(unsigned char* __restrict__ active, const Real4<R>* __restrict__ pos,
+                   const int32_t* __restrict__ orig, int64_t n, Consts<R> c, Control* ctrl) {
   const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
   bool act = false;
   if (i < n) {
     act = !(pos[i].w >= c.huge);
-    if (active) active[i] = act ? 1 : 0;
+    if (active) active[orig ? orig[i] : i] = act ? 1 : 0;
   }
   const unsigned m = __ballot_sync(0xffffffffu, act);
   if ((threadIdx.x & 31) == 0 && m) atomicAdd(&ctrl->n_active, (unsigned long long)__popc(m));

@@ -1,0 +1,18 @@
+"""Quick timing probe of one configuration: python tools/probe_cells.py N PRECISION [allpairs|cells] [steps]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import particle_simulation_b200 as P
+from particle_simulation_b200 import generate as G
+
+n = int(sys.argv[1]); prec = int(sys.argv[2])
+algo = sys.argv[3] if len(sys.argv) > 3 else "cells"
+steps = int(sys.argv[4]) if len(sys.argv) > 4 else 100
+ids, pos, vel, area = G.synthetic(n)
+sim = P.Simulation(P.make_params(length_of_area=area), ids, pos, vel, prec)
+sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED if algo == "cells" else P.FORCE_ALL_PAIRS)
+sim.advance(30 if algo == "cells" else 3)
+ms = sim.advance_timed(steps) / steps
+c = sim.counters()
+print(f"{algo} n={n} f{prec*8} ms/step={ms:.4f} steps/s={1e3/ms:.1f} pairs/s={n*(n-1)/ms*1e3:.3e} rebuilds={c.rebuilds}")
