@@ -105,7 +105,8 @@ psim_status psim_create(const psim_params* params, int precision, int64_t n,
  * `world` (the reference's thread slices, program_...:305-323, one per GPU).
  * All ranks pass the full particle arrays.  nccl_unique_id is the 128-byte
  * ncclUniqueId produced by psim_comm_unique_id on rank 0 and distributed by the
- * host (torch.distributed, MPI, a file ...). */
+ * host (torch.distributed, MPI, a file ...).  Every sharded handle owns its own
+ * communicator: use a fresh id per handle. */
 psim_status psim_create_sharded(const psim_params* params, int precision, int64_t n,
                                 const int32_t* id, const void* pos, const void* vel,
                                 int device, int rank, int world,

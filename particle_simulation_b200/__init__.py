@@ -6,7 +6,7 @@ fortran_src/module_stoermer_verlet_method.f08, driven as in
 fortran_src/program_particle_simulation_openmp.f08.  The product is the CUDA
 library behind include/psim.h (csrc/); this package is the thin Python host.
 """
-from . import formats, generate, native  # noqa: F401
+from . import formats, generate, native, sharding  # noqa: F401
 from .native import (  # noqa: F401
     FORCE_ALL_PAIRS, FORCE_CELL_BINNED, OPT_EXACT_DIFF_FILTER, OPT_FORCE_ALGO, OPT_FUSED_STEP,
     OPT_KERNEL_TIMING, Params, PsimError, Simulation, compute_forces, make_params,

@@ -1,0 +1,85 @@
+"""Run under torchrun with N >= 2 ranks (one GPU each): the i-sharded path with the
+per-step NCCL position all-gather must reproduce the oracle (and hence the
+single-GPU path), including deactivation decisions taken from the merged
+per-rank displacement maxima."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    import particle_simulation_b200 as P
+    from particle_simulation_b200 import native, sharding
+    from oracle import oracle_py as O
+    from conftest import two_cubes
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def fresh_uid():
+        # one ncclUniqueId per communicator, i.e. per sharded handle
+        buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            buf.copy_(torch.frombuffer(bytearray(native.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        return bytes(buf.cpu().numpy().tobytes())
+
+    ok = True
+    for precision, xtol in ((8, 1e-9), (4, 2e-4)):
+        for scenario in ("calm", "leaving"):
+            if scenario == "calm":
+                ids, pos, vel = two_cubes()
+                kw = {}
+            else:
+                ids, pos, vel = two_cubes(side=4, speed=40.0, origin=3.0)
+                kw = dict(length_of_area=(30.0, 30.0, 30.0), delta_t=0.002)
+            n = len(ids)
+            sim = P.Simulation(P.make_params(**kw), ids, pos, vel, precision, device=local, rank=rank, world=world,
+                               nccl_unique_id=fresh_uid())
+            assert (sim.i_lo, sim.i_hi) == sharding.shard_bounds(n, rank, world)
+            o = O.Oracle(O.make_params(**kw), precision, ids, pos, vel)
+            for chunk in (1, 30, 29):
+                sim.advance(chunk); o.advance(chunk)
+            _, x, v, a = sim.frame()
+            _, xr, vr, ar = o.frame()
+            # velocities: every rank fills its own slice; merge in rank order
+            parts = [torch.zeros((n, 3), dtype=torch.float64, device="cuda") for _ in range(world)]
+            dist.all_gather(parts, torch.from_numpy(v.astype(np.float64)).cuda())
+            bounds = [sharding.shard_bounds(n, r, world) for r in range(world)]
+            vm = sharding.merge_owned([p.cpu().numpy() for p in parts], bounds, n)
+            # the violent f32 scenario is chaotic beyond ~50 steps: flags and schedule only
+            compare_xv = not (scenario == "leaving" and precision == 4)
+            good = np.array_equal(a, ar) and sim.counters().rebuilds == o.rebuilds
+            keep = ar.astype(bool)      # ejected particles carry |x| ~ 1e10: compare the active ones
+            if compare_xv and keep.any():
+                good = good and np.abs(x[keep] - xr[keep]).max() <= 50 * xtol and np.abs(vm[keep] - vr[keep]).max() <= 5000 * xtol
+            if scenario == "leaving":
+                good = good and (ar == 0).any()
+            if not good:
+                ix = np.unravel_index(np.abs(x - xr).argmax(), x.shape); iv = np.unravel_index(np.abs(vm - vr).argmax(), vm.shape)
+                print("rank %d detail: x[%s]=%r ref %r act %d/%d | v[%s]=%r ref %r act %d/%d flags_equal=%s" % (
+                    rank, ix, x[ix], xr[ix], a[ix[0]], ar[ix[0]], iv, vm[iv], vr[iv], a[iv[0]], ar[iv[0]], np.array_equal(a, ar)), flush=True)
+                print("rank %d: MISMATCH precision=%d scenario=%s dx=%g dv=%g rebuilds %d vs %d" % (
+                    rank, precision, scenario, np.abs(x - xr).max(), np.abs(vm - vr).max(),
+                    sim.counters().rebuilds, o.rebuilds))
+            ok = ok and good
+            sim.close(); o.close()
+    t = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0 and t.item() == 1.0:
+        print("sharded check ok (%d ranks)" % world)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if t.item() == 1.0 else 1)
+
+
+if __name__ == "__main__":
+    main()
