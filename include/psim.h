@@ -72,8 +72,11 @@ typedef enum psim_option {
   PSIM_OPT_FORCE_ALGO = 0,      /* psim_force_algo */
   PSIM_OPT_FUSED_STEP = 1,      /* 1: force+kick+drift in one kernel (default), 0: separate kernels */
   PSIM_OPT_KERNEL_TIMING = 2,   /* 1: bracket every force-kernel launch with CUDA events */
-  PSIM_OPT_EXACT_DIFF_FILTER = 3 /* 1: all-pairs distance test in difference form (7 pipe ops/pair)
-                                    instead of the norm-expansion pre-filter (3 FMAs/pair) */
+  PSIM_OPT_EXACT_DIFF_FILTER = 3 /* all-pairs kernel variant: 0 (default) cluster kernel with the
+                                    norm-expansion pre-filter (3 FMAs per ordered pair); 1 first-generation
+                                    kernel with the distance test in difference form (3 sub, 1 mul, 2 FMA,
+                                    1 compare per pair: the literal reading of stoermer:117-121);
+                                    2 first-generation kernel with the pre-filter */
 } psim_option;
 
 typedef struct psim_counters {

@@ -14,11 +14,13 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "psim_allpairs.cuh"
+#include "psim_allpairs2.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -102,6 +104,15 @@ static Consts<R> derive_consts(const psim_params& p) {
   c.one_minus_k = (R)1 - (R)32 * eps;
   c.cut2_pad = c.r_cut * c.r_cut * ((R)1 + (R)32 * eps);
   c.huge = RealTraits<R>::huge;
+  c.boff = (R)0;
+  c.bslack = (R)0;
+  if (sizeof(R) == 8) {
+    // |x|^2 of anything that can be active: inside the box plus one cell of excursion
+    R b = 0;
+    for (int d = 0; d < 3; ++d) b += (c.area[d] + c.min_cell) * (c.area[d] + c.min_cell);
+    c.boff = b;
+    c.bslack = (R)16 * eps * b;
+  }
   c.slices = std::max<int>(1, p.nb_of_threads);
   return c;
 }
@@ -137,6 +148,11 @@ class SimT final : public psim_sim {
   static constexpr int T = 128;                                   // threads per force block = j-tile
   static constexpr int RI = 2;                                    // i-particles per thread
   static constexpr int TS = 256;                                  // threads of the streaming kernels
+  static constexpr int MAX_CLUSTER = 8;                           // portable cluster size limit
+  int variant = 0;      // 0: cluster kernel (default), 1: difference-form v1 kernel, 2: pre-filter v1 kernel
+  int ri_sel = 8;       // i-particles per lane of the production all-pairs kernel (8, or 4 for tuning)
+  int cluster_forced = 0;
+  int sm_count = 148;
 
   int device = 0;
   int64_t n = 0, n_pad = 0, shard = 0, i_lo = 0, i_hi = 0;
@@ -213,6 +229,12 @@ class SimT final : public psim_sim {
     device = device_;
     PSIM_CK(cudaSetDevice(device));
     n = n_; rank = rank_; world = world_;
+    PSIM_CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (const char* e = std::getenv("PSIM_RI")) ri_sel = std::atoi(e) == 4 ? 4 : 8;           // tuning knobs
+    if (const char* e = std::getenv("PSIM_CLUSTER")) {
+      const int v = std::atoi(e);
+      if (v == 1 || v == 2 || v == 4 || v == 8) cluster_forced = v;
+    }
     c = derive_consts<R>(p);
     mass = p.mass;
     if (!(c.min_cell >= c.r_cut)) {
@@ -221,7 +243,7 @@ class SimT final : public psim_sim {
       g_last_error = "LENGTH_OF_CELL smaller than R_CUT*SIGMA is not supported";
       return PSIM_ERR_UNSUPPORTED;
     }
-    const int64_t gran = (int64_t)T * world;
+    const int64_t gran = (int64_t)T * MAX_CLUSTER * world;   // every rank's j range splits into 1..8 equal tile runs
     n_pad = (n + gran - 1) / gran * gran;
     shard = n_pad / world;
     i_lo = std::min<int64_t>(n, shard * rank);
@@ -232,7 +254,7 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMalloc(&pos[0], rec)); PSIM_CK(cudaMalloc(&pos[1], rec));
     PSIM_CK(cudaMalloc(&vel, rec)); PSIM_CK(cudaMalloc(&f_old, rec));
     PSIM_CK(cudaMalloc(&f_new, rec)); PSIM_CK(cudaMalloc(&disp, rec));
-    top2_cap = std::max<int64_t>(blocks(n_pad, TS), blocks(n_pad, T)) + 8;
+    top2_cap = std::max<int64_t>(blocks(n_pad, TS), blocks(n_pad, 128) * MAX_CLUSTER) + 8;
     PSIM_CK(cudaMalloc(&top2_part, sizeof(R) * 2 * top2_cap));
     PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * world));
     PSIM_CK(cudaMalloc(&ctrl, sizeof(Control)));
@@ -288,9 +310,45 @@ class SimT final : public psim_sim {
   }
 
   template <int MODE>
-  void launch_allpairs(const StepArgs<R>& a, int64_t grid) {
-    if (exact_diff) allpairs_step_kernel<R, T, RI, MODE, true><<<grid, T, 0, stream>>>(a);
+  void launch_v1(const StepArgs<R>& a, int64_t grid) {
+    if (variant == 1) allpairs_step_kernel<R, T, RI, MODE, true><<<grid, T, 0, stream>>>(a);
     else allpairs_step_kernel<R, T, RI, MODE, false><<<grid, T, 0, stream>>>(a);
+  }
+
+  // cluster size: smallest power of two that gives every SM about four blocks or more
+  int pick_cluster(int64_t itiles) const {
+    if (cluster_forced) return cluster_forced;
+    int S = 1;
+    while (S < MAX_CLUSTER && itiles * S < (int64_t)sm_count * 4) S *= 2;
+    return S;
+  }
+
+  template <int MODE, int RIv>
+  cudaError_t launch_cluster(const StepArgs<R>& a, int64_t* grid_out) {
+    const int64_t itiles = blocks(i_hi - i_lo, 32 * RIv);
+    const int S = pick_cluster(itiles);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(itiles * S));
+    cfg.blockDim = dim3(T);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = S; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr; cfg.numAttrs = 1;
+    *grid_out = itiles * S;
+    return cudaLaunchKernelEx(&cfg, allpairs_warp_kernel<R, RIv, MODE>, a, S);
+  }
+
+  template <int MODE>
+  psim_status launch_allpairs(const StepArgs<R>& a, int64_t* grid_out) {
+    if (variant != 0) {
+      *grid_out = blocks(i_hi - i_lo, T * RI);
+      launch_v1<MODE>(a, *grid_out);
+      return PSIM_OK;
+    }
+    if (ri_sel == 4) PSIM_CK((launch_cluster<MODE, 4>(a, grid_out)));
+    else PSIM_CK((launch_cluster<MODE, 8>(a, grid_out)));
+    return PSIM_OK;
   }
 
   psim_status launch_force(int mode) {
@@ -313,10 +371,12 @@ class SimT final : public psim_sim {
       if (st != PSIM_OK) return st;
     } else {
       const StepArgs<R> a = step_args();
-      const int64_t grid = blocks(i_hi - i_lo, T * RI);
-      if (mode == MODE_FORCE) launch_allpairs<MODE_FORCE>(a, grid);
-      else if (mode == MODE_FORCE_KICK) launch_allpairs<MODE_FORCE_KICK>(a, grid);
-      else { launch_allpairs<MODE_FORCE_KICK_DRIFT>(a, grid); top2_count = grid; }
+      int64_t grid = 0;
+      psim_status st;
+      if (mode == MODE_FORCE) st = launch_allpairs<MODE_FORCE>(a, &grid);
+      else if (mode == MODE_FORCE_KICK) st = launch_allpairs<MODE_FORCE_KICK>(a, &grid);
+      else { st = launch_allpairs<MODE_FORCE_KICK_DRIFT>(a, &grid); top2_count = grid; }
+      if (st != PSIM_OK) return st;
       ++launches;
     }
     ++force_launches;
@@ -487,7 +547,9 @@ class SimT final : public psim_sim {
         algo = (int)value; cells.invalidate(); return PSIM_OK;
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
-      case PSIM_OPT_EXACT_DIFF_FILTER: exact_diff = value != 0; return PSIM_OK;
+      case PSIM_OPT_EXACT_DIFF_FILTER:
+        if (value < 0 || value > 2) return PSIM_ERR_INVALID_ARGUMENT;
+        variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
     }
   }

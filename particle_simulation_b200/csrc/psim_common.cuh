@@ -64,6 +64,8 @@ struct Consts {
   R one_minus_k;   // weight scale: w = |x|^2 * (1 - k)
   R cut2_pad;      // r_cut^2 (1 + delta): upper bound of what can pass the exact test
   R huge;
+  R boff;          // FP64 cluster kernel: offset B that keeps est + B non-negative (0 for FP32)
+  R bslack;        // absolute slack covering the roundings B introduces
   int slices;      // NB_OF_THREADS: slices of the rebuild trigger
 };
 

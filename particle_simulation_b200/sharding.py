@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import numpy as np
 
-TILE = 128   # SimT::T
+TILE = 128 * 8   # SimT::T x SimT::MAX_CLUSTER: a rank's j range splits into up to 8 equal tile runs
 
 
 def padded_size(n: int, world: int, tile: int = TILE) -> int:
