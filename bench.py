@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--algo", default="allpairs", choices=("allpairs", "cells"))
     ap.add_argument("--impl", default="b200", choices=("b200", "reference"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cells", action="store_true", help="skip the cell-binned companion measurement")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--exact-diff", action="store_true", help="difference-form distance test (no pre-filter)")
     return ap.parse_args()
@@ -250,6 +251,7 @@ def main():
         sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
     if args.exact_diff:
         sim.set_option(P.OPT_EXACT_DIFF_FILTER, 1)
+        sim.set_positions(pos.astype(native.rt(prec)))
     pairs_total = float(n) * (n - 1)
     n_own = sim.i_hi - sim.i_lo
 
@@ -279,7 +281,14 @@ def main():
     kernel_ms = (k1.force_ms - k0.force_ms) / max(1, n_timed)
     flops_launch = 8.0 * n_own * (n - 1) + 15.0 * pin_own
     achieved = flops_launch / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else 0.0
-    peak, peak_mhz = native.measure_fma_peak(prec, local_rank)
+    peak64, _ = native.measure_fma_peak(8, local_rank)
+    peak32, _ = native.measure_fma_peak(4, local_rank)
+    # Which pipe bounds the kernel.  The production all-pairs kernel runs its distance tests as
+    # packed FP32 FMAs for BOTH working precisions (exact path in the working precision), so it is
+    # bound by the FP32 FMA pipe; the first-generation difference-form kernel (--exact-diff) and the
+    # cell-binned kernel in f64 spend their time on the FP64 pipe.
+    fp32_bound = (prec == 4) or (args.algo == "allpairs" and not args.exact_diff)
+    peak = peak32 if fp32_bound else peak64
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
@@ -287,15 +296,24 @@ def main():
     except Exception:
         pass
     bytes_launch = n_own * (4 * prec) * 6.0 + n * 4 * prec    # owned records r/w + one pass over all positions
+    executed = 6.0 * n_own * (n - 1) / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 and args.algo == "allpairs" else None
     roofline = {
-        "bound": "fp64_fma" if prec == 8 else "fp32_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+        "bound": "fp32_fma" if fp32_bound else "fp64_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
         "frac": achieved / peak if peak else None, "traffic": traffic,
-        "peak_source": "psim_measure_fma_peak: dependent-free FMA loop on all SMs, this run (of measured)",
-        "kernel": "allpairs_step_kernel" if args.algo == "allpairs" else "cell_force_kernel",
+        "peak_source": "psim_measure_fma_peak: dependent-free FMA loop on all SMs, this run (of measured; "
+                       "MEASURED_PEAKS.json has no vector-FMA figure)",
+        "kernel": ("allpairs_warp_kernel" if not args.exact_diff else "allpairs_step_kernel") if args.algo == "allpairs" else "cell_force_kernel",
         "kernel_ms": kernel_ms, "launches_timed": int(n_timed), "flops_per_launch": flops_launch,
+        "flops_accounting": "SURVEY.md 8(d): 8 per ordered pair tested + 15 per ordered pair in range",
         "pairs_in_range_per_step": int(sum_over_ranks(pin_own)),
         "share_of_step": kernel_ms / (ms / args.steps) if ms > 0 else None,
         "hbm_bytes_per_launch_algorithmic": bytes_launch,
+        "fp64_fma_peak": peak64, "fp32_fma_peak": peak32,
+        "frac_of_fp64_fma_peak": achieved / peak64 if peak64 else None,
+        "executed_filter_tflops": executed,
+        "executed_frac": (executed / peak) if (executed and peak) else None,
+        "note": "frac uses the survey's 8-flop difference-form count per pair; the kernel's norm-expansion filter "
+                "executes 3 FMAs = 6 flops per pair (executed_*), on the FP32 pipe, so frac_of_fp64_fma_peak can exceed 1",
     }
 
     # ---- e2e: the force operator with host buffers through the C ABI ----
@@ -332,6 +350,22 @@ def main():
                          (n * 4 * prec * 6 / 1e6)},
         "roofline": roofline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }
+
+    if world == 1 and args.algo == "allpairs" and not args.no_cells:
+        # the same job through the cell-binned path: what a user who wants
+        # timesteps/s would select; single GPU in this version
+        cs = P.Simulation(params, ids, pos, vel, prec, device=local_rank)
+        cs.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
+        cs.advance(30)
+        csteps = max(args.steps, 200)
+        cms = cs.advance_timed(csteps)
+        cc = cs.counters()
+        line["cell_binned"] = {"timesteps_per_s": csteps / (cms * 1e-3), "ms_per_step": cms / csteps,
+                               "value": pairs_total * csteps / (cms * 1e-3), "unit": "pair-interactions/s",
+                               "steps": csteps, "rebuilds": int(cc.rebuilds),
+                               "note": "equivalent rate: N(N-1) x timesteps/s; the path tests only the 27-cell "
+                                       "neighbourhood of each particle"}
+        cs.close()
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
