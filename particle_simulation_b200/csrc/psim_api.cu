@@ -254,7 +254,7 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMalloc(&pos[0], rec)); PSIM_CK(cudaMalloc(&pos[1], rec));
     PSIM_CK(cudaMalloc(&vel, rec)); PSIM_CK(cudaMalloc(&f_old, rec));
     PSIM_CK(cudaMalloc(&f_new, rec)); PSIM_CK(cudaMalloc(&disp, rec));
-    top2_cap = std::max<int64_t>(blocks(n_pad, TS), blocks(n_pad, 128) * MAX_CLUSTER) + 8;
+    top2_cap = std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 128) * MAX_CLUSTER) + 8;
     PSIM_CK(cudaMalloc(&top2_part, sizeof(R) * 2 * top2_cap));
     PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * world));
     PSIM_CK(cudaMalloc(&ctrl, sizeof(Control)));

@@ -10,11 +10,8 @@
 // rebuilds the order is kept: a cell is at least r_cut + dr_max_tolerable wide
 // (stoermer:75), the same skin argument that keeps the reference's lists valid.
 //
-// The force kernel gives one thread one particle.  Phase 1 scans the nine runs
-// with the 3-FMA pre-filter and appends the few survivors to a per-thread queue
-// in shared memory (in-range pairs are ~6 % of the neighbourhood, far too dense
-// for a divergent branch per pair); phase 2 walks the queue with the exact pair
-// term.  Sums run in ascending slot order: deterministic.
+// The force kernel gives one lane one particle and one warp 32 consecutive
+// slots; see cell_force_kernel below.
 //
 // Everything here is conditional ON THE DEVICE: the re-binning kernels read
 // the rebuild flag from the control block and return at once when it is clear,
@@ -22,6 +19,7 @@
 #pragma once
 
 #include "psim_allpairs.cuh"
+#include "psim_allpairs2.cuh"
 #include "psim_integrate.cuh"
 
 namespace psim {
@@ -155,93 +153,123 @@ __global__ void iota_kernel(int32_t* p, int64_t n) {
 
 // The force pass over the binned state.
 //
-// A block owns T consecutive slots, i.e. the particles of a short run of cells
-// cmin..cmax.  For each of the nine (dy, dz) offsets the union of its threads'
-// neighbour cells is ONE contiguous run of slots (cells cmin-1+off ..
-// cmax+1+off in linear cell order; a run that wraps around a grid edge only
-// adds far-away particles, which the filter rejects).  The block stages that
-// run into shared memory in chunks of CAP records and every thread scans the
-// part of it that belongs to its own three cells.
-template <class R, int T, int MODE, int QCAP, int CAP>
+// A WARP owns 32 consecutive slots, i.e. the particles of one or two cells
+// cmin..cmax (one particle per lane).  For each of the nine (dy, dz) offsets the
+// union of its lanes' neighbour cells is ONE contiguous run of slots (cells
+// cmin-1+off .. cmax+1+off in linear cell order; a run that wraps around a grid
+// edge only adds far-away particles, which the filter rejects).  The warp walks
+// that run in 32-record tiles, one record per lane, staged as float SoA behind
+// __syncwarp — no block barrier, no per-lane loop bounds, broadcast reads.
+//
+// Phase 1 is the packed-FP32 conservative filter of psim_allpairs2.cuh (FFMA2:
+// two j per instruction); a lane appends the slots that pass to its private
+// queue in shared memory.  In-range pairs are ~6 % of the neighbourhood: far too
+// dense for a divergent exact evaluation per hit, cheap enough to queue.
+// Phase 2 walks the queue with the exact pair term in the working precision.
+// Sums run in ascending slot order: deterministic.
+template <class R, int MODE, int QCAP, int T>
 __global__ void __launch_bounds__(T)
 cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
                   const int32_t* __restrict__ cell_start, int ncell, int64_t n) {
-  __shared__ int32_t queue[QCAP * T];
-  __shared__ Real4<R> tile[CAP];
-  __shared__ int s_cmin, s_cmax;
+  constexpr int W = T / 32, TJ = 32;
+  __shared__ int32_t queue[(QCAP + 1) * T];   // one spare row: the branch-free append always stores
+  __shared__ __align__(16) float tx[W][2][TJ], ty[W][2][TJ], tz[W][2][TJ], tw[W][2][TJ];
   const Consts<R>& c = a.c;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t k = (int64_t)blockIdx.x * T + tid;
+  const float rcut = (float)c.r_cut;
+  const float cut2f = (float)c.cut2_pad * (1.0f + 1.0e-6f);
 
-  R xi = 0, yi = 0, zi = 0, ax = 0, ay = 0, az = 0, cut = -c.huge;
-  R fx = 0, fy = 0, fz = 0;
+  R xi = 0, yi = 0, zi = 0, fx = 0, fy = 0, fz = 0;
+  float fxi = 0.f, fyi = 0.f, fzi = 0.f, cutf = -1.0e30f;
   int cell = ncell;
   if (k < n) {
     cell = cell_of[k];
     const Real4<R> p = a.pos_cur[k];
     if (cell < ncell && !(p.w >= c.huge)) {
       xi = p.x; yi = p.y; zi = p.z;
-      ax = (R)-2 * xi; ay = (R)-2 * yi; az = (R)-2 * zi;
-      cut = c.cut2_pad - p.w;
+      const FilterRec f = filter_record(p, c, rcut);
+      fxi = f.x; fyi = f.y; fzi = f.z; cutf = cut2f - f.w;
     } else {
       cell = ncell;
     }
   }
-  if (tid == 0) { s_cmin = ncell; s_cmax = -1; }
-  __syncthreads();
-  if (cell < ncell) { atomicMin(&s_cmin, cell); atomicMax(&s_cmax, cell); }
-  __syncthreads();
-  const int cmin = s_cmin, cmax = s_cmax;
+  // cells spanned by this warp's active slots
+  int cmin = cell < ncell ? cell : INT_MAX, cmax = cell < ncell ? cell : -1;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    cmin = min(cmin, __shfl_xor_sync(0xffffffffu, cmin, off));
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, off));
+  }
 
   int cnt = 0;
+  // Two queue entries per trip: independent chains (sqrt, two divisions each) that the
+  // scheduler interleaves; the additions keep queue order, so the sum stays deterministic.
   auto flush = [&]() {
-    if (cnt == 0) return;
-    Real4<R> q = a.pos_cur[queue[tid]];
-    for (int e = 0; e < cnt; ++e) {
-      const Real4<R> qc = q;
-      if (e + 1 < cnt) q = a.pos_cur[queue[(e + 1) * T + tid]];     // next record in flight
-      pair_force(xi, yi, zi, qc.x, qc.y, qc.z, c, fx, fy, fz);
+    int e = 0;
+    for (; e + 1 < cnt; e += 2) {
+      const int j0 = queue[e * T + tid], j1 = queue[(e + 1) * T + tid];
+      const Real4<R> q0 = a.pos_cur[j0], q1 = a.pos_cur[j1];
+      R ax0 = (R)0, ay0 = (R)0, az0 = (R)0, ax1 = (R)0, ay1 = (R)0, az1 = (R)0;
+      if (j0 != (int)k) pair_force(xi, yi, zi, q0.x, q0.y, q0.z, c, ax0, ay0, az0);
+      if (j1 != (int)k) pair_force(xi, yi, zi, q1.x, q1.y, q1.z, c, ax1, ay1, az1);
+      // pair_force subtracted each force from 0; apply them in order
+      fx = r_add(r_add(fx, ax0), ax1); fy = r_add(r_add(fy, ay0), ay1); fz = r_add(r_add(fz, az0), az1);
+    }
+    if (e < cnt) {
+      const int j0 = queue[e * T + tid];
+      const Real4<R> q = a.pos_cur[j0];
+      if (j0 != (int)k) pair_force(xi, yi, zi, q.x, q.y, q.z, c, fx, fy, fz);
     }
     cnt = 0;
   };
 
-  if (cmax >= 0) {                       // the block has at least one active particle
-    const int nx = c.nc[0], ny = c.nc[1], nz = c.nc[2];
-    const int cx = cell % nx, cy = (cell / nx) % ny, cz = cell / (nx * ny);   // 0-based (unused if inactive)
-    const int x0 = max(cx - 1, 0), x1 = min(cx + 1, nx - 1);
+  if (cmax >= 0) {                       // warp-uniform: the warp has at least one active particle
+    const int nx = c.nc[0], ny = c.nc[1];
+    auto stage = [&](int buf, int j, int tb) {
+      FilterRec f; f.x = f.y = f.z = 0.f; f.w = 1.0e30f;
+      if (j < tb) f = filter_record(a.pos_cur[j], c, rcut);
+      tx[warp][buf][lane] = -2.0f * f.x; ty[warp][buf][lane] = -2.0f * f.y; tz[warp][buf][lane] = -2.0f * f.z;
+      tw[warp][buf][lane] = f.w;
+    };
+    int next_cell = 0;                   // runs are visited in ascending cell order: never scan a cell twice
+    int qidx = tid;                      // queue slot of this lane's next entry: cnt * T + tid
     for (int dz = -1; dz <= 1; ++dz) {
       for (int dy = -1; dy <= 1; ++dy) {
         const int off = nx * (dy + ny * dz);
-        const int blo = max(cmin - 1 + off, 0), bhi = min(cmax + 1 + off, ncell - 1);
-        if (bhi < blo) continue;         // block-uniform
-        const int ta_all = cell_start[blo], tb_all = cell_start[bhi + 1];
-        // this thread's own run inside the block's run
-        int ja = 0, jb = 0;
-        const int y = cy + dy, z = cz + dz;
-        if (cell < ncell && y >= 0 && y < ny && z >= 0 && z < nz) {
-          const int row = nx * (y + ny * z);
-          ja = cell_start[row + x0];
-          jb = cell_start[row + x1 + 1];
-        }
-        for (int ta = ta_all; ta < tb_all; ta += CAP) {
-          const int tb = min(ta + CAP, tb_all);
-          __syncthreads();               // previous chunk fully consumed
-          for (int t = ta + tid; t < tb; t += T) tile[t - ta] = a.pos_cur[t];
-          __syncthreads();
-          const int lo = max(ja, ta), hi = min(jb, tb);
-          for (int j = lo; j < hi; j += 4) {
-            Real4<R> q[4];
+        const int blo = max(max(cmin - 1 + off, 0), next_cell), bhi = min(cmax + 1 + off, ncell - 1);
+        if (bhi < blo) continue;         // warp-uniform
+        next_cell = bhi + 1;
+        const int ta = cell_start[blo], tb = cell_start[bhi + 1];
+        if (tb <= ta) continue;
+        int buf = 0;
+        stage(0, ta + lane, tb);
+        __syncwarp();
+        for (int t0 = ta; t0 < tb; t0 += TJ) {
+          // room for a whole tile in every lane's queue, decided for the warp as one
+          if (__any_sync(0xffffffffu, cnt > QCAP - TJ)) { flush(); qidx = tid; }
+          if (t0 + TJ < tb) stage(buf ^ 1, t0 + TJ + lane, tb);
+          const float2 px = make_float2(fxi, fxi), py = make_float2(fyi, fyi), pz = make_float2(fzi, fzi);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) q[u] = tile[min(j + u, hi - 1) - ta];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const R est = r_fma(ax, q[u].x, r_fma(ay, q[u].y, r_fma(az, q[u].z, q[u].w)));
-              if (est < cut && j + u < hi && j + u != (int)k) {
-                queue[cnt * T + tid] = j + u;
-                if (++cnt == QCAP) flush();
-              }
-            }
+          for (int jj = 0; jj < TJ; jj += 4) {
+            const float4 X = *reinterpret_cast<const float4*>(&tx[warp][buf][jj]);
+            const float4 Y = *reinterpret_cast<const float4*>(&ty[warp][buf][jj]);
+            const float4 Z = *reinterpret_cast<const float4*>(&tz[warp][buf][jj]);
+            const float4 Wt = *reinterpret_cast<const float4*>(&tw[warp][buf][jj]);
+            const float2 e01 = __ffma2_rn(px, make_float2(X.x, X.y), __ffma2_rn(py, make_float2(Y.x, Y.y),
+                               __ffma2_rn(pz, make_float2(Z.x, Z.y), make_float2(Wt.x, Wt.y))));
+            const float2 e23 = __ffma2_rn(px, make_float2(X.z, X.w), __ffma2_rn(py, make_float2(Y.z, Y.w),
+                               __ffma2_rn(pz, make_float2(Z.z, Z.w), make_float2(Wt.z, Wt.w))));
+            // branch-free append: always store, advance only on a hit
+            const int j = t0 + jj;
+            queue[qidx] = j;     qidx += e01.x < cutf ? T : 0;
+            queue[qidx] = j + 1; qidx += e01.y < cutf ? T : 0;
+            queue[qidx] = j + 2; qidx += e23.x < cutf ? T : 0;
+            queue[qidx] = j + 3; qidx += e23.y < cutf ? T : 0;
           }
+          cnt = (qidx - tid) / T;
+          __syncwarp();
+          buf ^= 1;
         }
       }
     }
@@ -255,9 +283,9 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
 
 template <class R>
 struct CellPath {
-  static constexpr int T = 128;
-  static constexpr int QCAP = 64;
-  static constexpr int CAP = 256;
+  static constexpr int T = 128;          // threads of the re-binning kernels
+  static constexpr int TF = 64;          // threads of the force kernel (two autonomous warps)
+  static constexpr int QCAP = 96;        // queue entries per lane
   int64_t launches = 0;
   int64_t n = 0, n_pad = 0;
   int ncell = 0;
@@ -335,13 +363,13 @@ struct CellPath {
     if (ensure(sim) != cudaSuccess) return PSIM_ERR_CUDA;
     if (!binned) rebin(sim, sim.pos[sim.cur], 0, true);
     const StepArgs<R> a = sim.step_args();
-    const unsigned grid = (unsigned)((n + T - 1) / T);
+    const unsigned grid = (unsigned)((n + TF - 1) / TF);
     if (mode == MODE_FORCE)
-      cell_force_kernel<R, T, MODE_FORCE, QCAP, CAP><<<grid, T, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
+      cell_force_kernel<R, MODE_FORCE, QCAP, TF><<<grid, TF, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
     else if (mode == MODE_FORCE_KICK)
-      cell_force_kernel<R, T, MODE_FORCE_KICK, QCAP, CAP><<<grid, T, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
+      cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF><<<grid, TF, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
     else {
-      cell_force_kernel<R, T, MODE_FORCE_KICK_DRIFT, QCAP, CAP><<<grid, T, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
+      cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF><<<grid, TF, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
       sim.top2_count = grid;
     }
     ++launches;
