@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(T)
 cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
                   const int32_t* __restrict__ cell_start, int ncell, int64_t n) {
   constexpr int W = T / 32, TJ = 32;
-  __shared__ int32_t queue[(QCAP + 1) * T];   // one spare row: the branch-free append always stores
+  __shared__ int32_t queue[QCAP * T];
   __shared__ __align__(16) float tx[W][2][TJ], ty[W][2][TJ], tz[W][2][TJ], tw[W][2][TJ];
   const Consts<R>& c = a.c;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -206,29 +206,35 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
   // Two queue entries per trip: independent chains (sqrt, two divisions each) that the
   // scheduler interleaves; the additions keep queue order, so the sum stays deterministic.
   auto flush = [&]() {
+    if (cnt == 0) return;
+    // software pipeline: the next two records are in flight while two pair terms are evaluated
+    int ja = queue[tid], jb = cnt > 1 ? queue[T + tid] : ja;
+    Real4<R> qa = a.pos_cur[ja], qb = a.pos_cur[jb];
     int e = 0;
     for (; e + 1 < cnt; e += 2) {
-      const int j0 = queue[e * T + tid], j1 = queue[(e + 1) * T + tid];
-      const Real4<R> q0 = a.pos_cur[j0], q1 = a.pos_cur[j1];
+      const int j0 = ja, j1 = jb;
+      const Real4<R> q0 = qa, q1 = qb;
+      if (e + 2 < cnt) { ja = queue[(e + 2) * T + tid]; qa = a.pos_cur[ja]; }
+      if (e + 3 < cnt) { jb = queue[(e + 3) * T + tid]; qb = a.pos_cur[jb]; }
       R ax0 = (R)0, ay0 = (R)0, az0 = (R)0, ax1 = (R)0, ay1 = (R)0, az1 = (R)0;
       if (j0 != (int)k) pair_force(xi, yi, zi, q0.x, q0.y, q0.z, c, ax0, ay0, az0);
       if (j1 != (int)k) pair_force(xi, yi, zi, q1.x, q1.y, q1.z, c, ax1, ay1, az1);
       // pair_force subtracted each force from 0; apply them in order
       fx = r_add(r_add(fx, ax0), ax1); fy = r_add(r_add(fy, ay0), ay1); fz = r_add(r_add(fz, az0), az1);
     }
-    if (e < cnt) {
-      const int j0 = queue[e * T + tid];
-      const Real4<R> q = a.pos_cur[j0];
-      if (j0 != (int)k) pair_force(xi, yi, zi, q.x, q.y, q.z, c, fx, fy, fz);
-    }
+    if (e < cnt && ja != (int)k) pair_force(xi, yi, zi, qa.x, qa.y, qa.z, c, fx, fy, fz);
     cnt = 0;
   };
 
   if (cmax >= 0) {                       // warp-uniform: the warp has at least one active particle
     const int nx = c.nc[0], ny = c.nc[1];
-    auto stage = [&](int buf, int j, int tb) {
-      FilterRec f; f.x = f.y = f.z = 0.f; f.w = 1.0e30f;
-      if (j < tb) f = filter_record(a.pos_cur[j], c, rcut);
+    auto fetch = [&](int j, int tb) {      // global load only: the conversion waits until the data is needed
+      Real4<R> p; p.x = p.y = p.z = (R)0; p.w = c.huge;
+      if (j < tb) p = a.pos_cur[j];
+      return p;
+    };
+    auto stage = [&](int buf, const Real4<R>& p) {
+      const FilterRec f = filter_record(p, c, rcut);
       tx[warp][buf][lane] = -2.0f * f.x; ty[warp][buf][lane] = -2.0f * f.y; tz[warp][buf][lane] = -2.0f * f.z;
       tw[warp][buf][lane] = f.w;
     };
@@ -243,13 +249,16 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
         const int ta = cell_start[blo], tb = cell_start[bhi + 1];
         if (tb <= ta) continue;
         int buf = 0;
-        stage(0, ta + lane, tb);
+        stage(0, fetch(ta + lane, tb));
         __syncwarp();
         for (int t0 = ta; t0 < tb; t0 += TJ) {
           // room for a whole tile in every lane's queue, decided for the warp as one
           if (__any_sync(0xffffffffu, cnt > QCAP - TJ)) { flush(); qidx = tid; }
-          if (t0 + TJ < tb) stage(buf ^ 1, t0 + TJ + lane, tb);
+          const bool more = t0 + TJ < tb;
+          Real4<R> pre;
+          if (more) pre = fetch(t0 + TJ + lane, tb);   // in flight during this tile's filter
           const float2 px = make_float2(fxi, fxi), py = make_float2(fyi, fyi), pz = make_float2(fzi, fzi);
+          unsigned hits = 0u;              // bit jj: record t0 + jj passed the filter for this lane
 #pragma unroll
           for (int jj = 0; jj < TJ; jj += 4) {
             const float4 X = *reinterpret_cast<const float4*>(&tx[warp][buf][jj]);
@@ -260,14 +269,20 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
                                __ffma2_rn(pz, make_float2(Z.x, Z.y), make_float2(Wt.x, Wt.y))));
             const float2 e23 = __ffma2_rn(px, make_float2(X.z, X.w), __ffma2_rn(py, make_float2(Y.z, Y.w),
                                __ffma2_rn(pz, make_float2(Z.z, Z.w), make_float2(Wt.z, Wt.w))));
-            // branch-free append: always store, advance only on a hit
-            const int j = t0 + jj;
-            queue[qidx] = j;     qidx += e01.x < cutf ? T : 0;
-            queue[qidx] = j + 1; qidx += e01.y < cutf ? T : 0;
-            queue[qidx] = j + 2; qidx += e23.x < cutf ? T : 0;
-            queue[qidx] = j + 3; qidx += e23.y < cutf ? T : 0;
+            if (e01.x < cutf) hits |= 1u << jj;
+            if (e01.y < cutf) hits |= 2u << jj;
+            if (e23.x < cutf) hits |= 4u << jj;
+            if (e23.y < cutf) hits |= 8u << jj;
+          }
+          // expand the tile's hit mask into this lane's queue (a few entries per tile)
+          while (hits) {
+            const int b = __ffs(hits) - 1;
+            hits &= hits - 1;
+            queue[qidx] = t0 + b;
+            qidx += T;
           }
           cnt = (qidx - tid) / T;
+          if (more) stage(buf ^ 1, pre);
           __syncwarp();
           buf ^= 1;
         }
