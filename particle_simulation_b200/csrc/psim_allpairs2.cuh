@@ -144,22 +144,25 @@ allpairs_warp_kernel(const StepArgs<R> a, const int S) {
   // --- j side: this warp's run of 32-record tiles ---
   // tiles are dealt round-robin to the S*W warps that share this i-tile, so that the
   // (spatially clustered) in-range pairs, i.e. the exact-path work, spread evenly
-  const int64_t ntiles = a.n_pad / TJ / (S * W);
-  const int64_t stride = (int64_t)S * W;
-  const int64_t tile0 = crank * W + warp;
+  // (32-bit tile arithmetic: n_pad < 2^31, and the hot loop has no registers to spare)
+  const int total_tiles = (int)(a.n_pad / TJ);
+  const int stride = S * W;
+  const int tile0 = crank * W + warp;
+  const int ntiles = tile0 < total_tiles ? (total_tiles - tile0 + stride - 1) / stride : 0;
   auto stage = [&](int buf, const Real4<R>& p) {
     const FilterRec f = filter_record(p, c, rcut);
     tx[warp][buf][lane] = -2.0f * f.x; ty[warp][buf][lane] = -2.0f * f.y; tz[warp][buf][lane] = -2.0f * f.z;
     tw[warp][buf][lane] = f.w;
   };
-  Real4<R> pre = a.pos_cur[tile0 * TJ + lane];
+  Real4<R> pre; pre.x = pre.y = pre.z = (R)0; pre.w = c.huge;
+  if (ntiles > 0) pre = a.pos_cur[tile0 * TJ + lane];
   stage(0, pre);
   __syncwarp();
   int buf = 0;
 
-  for (int64_t jt = 0; jt < ntiles; ++jt) {
+  for (int jt = 0; jt < ntiles; ++jt) {
     if (jt + 1 < ntiles) pre = a.pos_cur[(tile0 + (jt + 1) * stride) * TJ + lane];
-    const int64_t j_base = (tile0 + jt * stride) * TJ;
+    const int j_base = (tile0 + jt * stride) * TJ;
 
 #pragma unroll
     for (int jj = 0; jj < TJ; jj += U) {
@@ -202,8 +205,9 @@ allpairs_warp_kernel(const StepArgs<R> a, const int S) {
   // --- meet the other j-splits: warps of this block, then blocks of the cluster ---
   cluster.sync();
   R first = (R)0, second = (R)0;
-  const int per = G / S;                     // every block finishes G/S particles
-  for (int li = crank * per + tid; li < (crank + 1) * per; li += 128) {
+  const int per = (G + S - 1) / S;           // every block finishes its share of the G particles
+  const int li_end = min((crank + 1) * per, G);
+  for (int li = crank * per + tid; li < li_end; li += 128) {
     const int64_t i = i_base + li;
     R sx = (R)0, sy = (R)0, sz = (R)0;
     for (int rr = 0; rr < S; ++rr) {         // fixed order: deterministic

@@ -150,7 +150,7 @@ class SimT final : public psim_sim {
   static constexpr int TS = 256;                                  // threads of the streaming kernels
   static constexpr int MAX_CLUSTER = 8;                           // portable cluster size limit
   int variant = 0;      // 0: cluster kernel (default), 1: difference-form v1 kernel, 2: pre-filter v1 kernel
-  int ri_sel = 8;       // i-particles per lane of the production all-pairs kernel (8, or 4 for tuning)
+  int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
   int sm_count = 148;
 
@@ -230,10 +230,10 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaSetDevice(device));
     n = n_; rank = rank_; world = world_;
     PSIM_CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
-    if (const char* e = std::getenv("PSIM_RI")) ri_sel = std::atoi(e) == 4 ? 4 : 8;           // tuning knobs
+    if (const char* e = std::getenv("PSIM_RI")) { const int v = std::atoi(e); if (v >= 6 && v <= 8) ri_sel = v; }   // tuning knobs
     if (const char* e = std::getenv("PSIM_CLUSTER")) {
       const int v = std::atoi(e);
-      if (v == 1 || v == 2 || v == 4 || v == 8) cluster_forced = v;
+      if (v >= 1 && v <= MAX_CLUSTER) cluster_forced = v;
     }
     c = derive_consts<R>(p);
     mass = p.mass;
@@ -254,7 +254,7 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMalloc(&pos[0], rec)); PSIM_CK(cudaMalloc(&pos[1], rec));
     PSIM_CK(cudaMalloc(&vel, rec)); PSIM_CK(cudaMalloc(&f_old, rec));
     PSIM_CK(cudaMalloc(&f_new, rec)); PSIM_CK(cudaMalloc(&disp, rec));
-    top2_cap = std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 128) * MAX_CLUSTER) + 8;
+    top2_cap = std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 32 * 6) * MAX_CLUSTER) + 8;
     PSIM_CK(cudaMalloc(&top2_part, sizeof(R) * 2 * top2_cap));
     PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * world));
     PSIM_CK(cudaMalloc(&ctrl, sizeof(Control)));
@@ -315,18 +315,40 @@ class SimT final : public psim_sim {
     else allpairs_step_kernel<R, T, RI, MODE, false><<<grid, T, 0, stream>>>(a);
   }
 
-  // cluster size: smallest power of two that gives every SM about four blocks or more
-  int pick_cluster(int64_t itiles) const {
-    if (cluster_forced) return cluster_forced;
-    int S = 1;
-    while (S < MAX_CLUSTER && itiles * S < (int64_t)sm_count * 4) S *= 2;
-    return S;
+  // Tiling of the production all-pairs kernel: RI i-particles per lane (i-tile = 32 RI) and S
+  // blocks per cluster (j split).  The kernel keeps 4 blocks per SM resident, so the grid runs in
+  // waves of 4 x SMs blocks; power-of-two tilings of power-of-two N leave the last wave 14 % empty
+  // (1024 blocks on 592 slots).  Choose the pair that fills its last wave best, preferring more i
+  // per lane (better FMA : shared-memory ratio) and enough blocks to cover every SM.
+  void pick_tiling(int* ri_out, int* s_out) const {
+    const int64_t slots = (int64_t)sm_count * 4;
+    double best = -1.0;
+    int best_ri = 8, best_s = 1;
+    if (!ri_sel && !cluster_forced && blocks(i_hi - i_lo, 32 * 8) >= slots) {
+      // more than a wave of full-size tiles: measured, the block scheduler backfills well enough
+      *ri_out = 8; *s_out = 1;
+      return;
+    }
+    for (int ri = 8; ri >= 6; --ri) {
+      if (ri_sel && ri != ri_sel) continue;
+      const int64_t itiles = blocks(i_hi - i_lo, 32 * ri);
+      for (int S = 1; S <= MAX_CLUSTER; ++S) {
+        if (cluster_forced && S != cluster_forced) continue;
+        const int64_t ctas = itiles * S;
+        const int64_t waves = (ctas + slots - 1) / slots;
+        double eff = (double)ctas / (double)(waves * slots);
+        eff *= 1.0 - 0.015 * (8 - ri);                       // fewer i per lane: a little less efficient
+        if (S > 1) eff *= 0.95 - 0.03 * (S - 1);            // measured: clusters schedule less densely, and more so the larger they are
+        if (ctas < slots / 2) eff *= 0.5;                    // leave no SM idle
+        if (eff > best) { best = eff; best_ri = ri; best_s = S; }
+      }
+    }
+    *ri_out = best_ri; *s_out = best_s;
   }
 
   template <int MODE, int RIv>
-  cudaError_t launch_cluster(const StepArgs<R>& a, int64_t* grid_out) {
+  cudaError_t launch_cluster(const StepArgs<R>& a, int S, int64_t* grid_out) {
     const int64_t itiles = blocks(i_hi - i_lo, 32 * RIv);
-    const int S = pick_cluster(itiles);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(itiles * S));
     cfg.blockDim = dim3(T);
@@ -346,8 +368,11 @@ class SimT final : public psim_sim {
       launch_v1<MODE>(a, *grid_out);
       return PSIM_OK;
     }
-    if (ri_sel == 4) PSIM_CK((launch_cluster<MODE, 4>(a, grid_out)));
-    else PSIM_CK((launch_cluster<MODE, 8>(a, grid_out)));
+    int ri = 8, S = 1;
+    pick_tiling(&ri, &S);
+    if (ri == 6) PSIM_CK((launch_cluster<MODE, 6>(a, S, grid_out)));
+    else if (ri == 7) PSIM_CK((launch_cluster<MODE, 7>(a, S, grid_out)));
+    else PSIM_CK((launch_cluster<MODE, 8>(a, S, grid_out)));
     return PSIM_OK;
   }
 
