@@ -48,7 +48,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--n", type=int, default=DEFAULT_N, help="particles (65536, 262144, 1048576 are SURVEY.md 8(d) shapes)")
+    ap.add_argument("--particles", "--n", dest="n", type=int, default=DEFAULT_N,
+                    help="particles (65536, 262144, 1048576 are SURVEY.md 8(d) shapes); under torchrun spell it "
+                         "--particles (torchrun's own parser trips over --n)")
     ap.add_argument("--precision", type=int, default=8, choices=(4, 8))
     ap.add_argument("--algo", default="allpairs", choices=("allpairs", "cells"))
     ap.add_argument("--impl", default="b200", choices=("b200", "reference"))
@@ -381,11 +383,12 @@ def main():
         except Exception as e:   # the baseline must never take the GPU line down
             line["cpu_baseline"] = {"error": repr(e)}
     sim.close()
-    if rank == 0:
-        print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+    if rank == 0:
+        sys.stderr.flush()
+        print(json.dumps(line), flush=True)      # the JSON line is the last thing this job prints
 
 
 if __name__ == "__main__":

@@ -21,7 +21,7 @@
 //    through is re-tested and evaluated in the WORKING precision with the
 //    reference's own operations, so the forces are the same as a pure
 //    FP64 / FP32 evaluation; the FP64 pipe is left to the in-range pairs only.
-// 3. Warps are autonomous: the four warps of a block own the same 256
+// 3. Warps are autonomous: the 4, 8 or 16 warps of a block own the same 32 RI
 //    i-particles but different runs of j tiles, each staging its own 32-record
 //    tile (one record per lane) behind __syncwarp — no block barrier in the hot
 //    loop.  Tiles are dealt round-robin, so the exact-path work (in-range pairs
@@ -98,16 +98,22 @@ __device__ __noinline__ void exact_group(const Real4<R>* __restrict__ pos, const
   }
 }
 
-template <class R, int RI, int MODE>
-__global__ void __launch_bounds__(128, 4)
+// Dynamic shared memory of allpairs_warp_kernel<R, RI, W, MODE>.
+template <class R, int RI, int W>
+constexpr size_t allpairs_warp_smem() { return sizeof(R) * W * 3 * 32 * RI; }
+
+template <class R, int RI, int W, int MODE>
+__global__ void __launch_bounds__(32 * W, 16 / W)
 allpairs_warp_kernel(const StepArgs<R> a, const int S) {
-  constexpr int W = 4;                       // warps per block = j-splits inside a block
+  // W warps per block = j-splits inside a block (4, 8 or 16; 16 warps per SM in every case)
+  constexpr int T = 32 * W;
   constexpr int G = 32 * RI;                 // i-particles per block (and per cluster)
   constexpr int TJ = 32;                     // j records per warp tile: one per lane
   constexpr int U = 8;                       // j records per filter group
   __shared__ __align__(16) float tx[W][2][TJ], ty[W][2][TJ], tz[W][2][TJ], tw[W][2][TJ];
   __shared__ float six[G], siy[G], siz[G], sic[G];      // float i-state for the exact path's re-filter
-  __shared__ R acc[W][3][G];                 // per-warp partial forces
+  extern __shared__ __align__(16) unsigned char dyn_smem[];
+  R (*acc)[3][G] = reinterpret_cast<R (*)[3][G]>(dyn_smem);   // acc[W][3][G]: per-warp partial forces
 
   cg::cluster_group cluster = cg::this_cluster();
   const Consts<R>& c = a.c;
@@ -118,16 +124,14 @@ allpairs_warp_kernel(const StepArgs<R> a, const int S) {
   const float cut2f = (float)c.cut2_pad * (1.0f + 1.0e-6f);
 
   // --- i side: float copies for the filter, in registers and (for the exact path) in shared memory
-  for (int li = tid; li < G; li += 128) {
+  for (int li = tid; li < G; li += T) {
     const int64_t i = i_base + li;
     FilterRec f; f.x = f.y = f.z = 0.f; f.w = 1.0e30f;
     if (i < a.i_hi) f = filter_record(a.pos_cur[i], c, rcut);
     six[li] = f.x; siy[li] = f.y; siz[li] = f.z;
     sic[li] = f.w >= 1.0e30f ? -1.0e30f : cut2f - f.w;
-    acc[0][0][li] = acc[0][1][li] = acc[0][2][li] = (R)0;
-    acc[1][0][li] = acc[1][1][li] = acc[1][2][li] = (R)0;
-    acc[2][0][li] = acc[2][1][li] = acc[2][2][li] = (R)0;
-    acc[3][0][li] = acc[3][1][li] = acc[3][2][li] = (R)0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) acc[w][0][li] = acc[w][1][li] = acc[w][2][li] = (R)0;
   }
   __syncthreads();
   float2 px[RI], py[RI], pz[RI];
@@ -207,7 +211,7 @@ allpairs_warp_kernel(const StepArgs<R> a, const int S) {
   R first = (R)0, second = (R)0;
   const int per = (G + S - 1) / S;           // every block finishes its share of the G particles
   const int li_end = min((crank + 1) * per, G);
-  for (int li = crank * per + tid; li < li_end; li += 128) {
+  for (int li = crank * per + tid; li < li_end; li += T) {
     const int64_t i = i_base + li;
     R sx = (R)0, sy = (R)0, sz = (R)0;
     for (int rr = 0; rr < S; ++rr) {         // fixed order: deterministic
@@ -222,7 +226,7 @@ allpairs_warp_kernel(const StepArgs<R> a, const int S) {
     if (i < a.i_hi) step_epilogue<R, MODE>(a, i, sx, sy, sz, first, second);
   }
   cluster.sync();                            // nobody leaves while its shared memory is still being read
-  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, 128>(first, second, a.top2_part);
+  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part);
 }
 
 }  // namespace psim

@@ -152,6 +152,7 @@ class SimT final : public psim_sim {
   int variant = 0;      // 0: cluster kernel (default), 1: difference-form v1 kernel, 2: pre-filter v1 kernel
   int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
+  int warps_forced = 0;
   int sm_count = 148;
 
   int device = 0;
@@ -231,6 +232,7 @@ class SimT final : public psim_sim {
     n = n_; rank = rank_; world = world_;
     PSIM_CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
     if (const char* e = std::getenv("PSIM_RI")) { const int v = std::atoi(e); if (v >= 6 && v <= 8) ri_sel = v; }   // tuning knobs
+    if (const char* e = std::getenv("PSIM_WARPS")) { const int v = std::atoi(e); if (v == 4 || v == 8 || v == 16) warps_forced = v; }
     if (const char* e = std::getenv("PSIM_CLUSTER")) {
       const int v = std::atoi(e);
       if (v >= 1 && v <= MAX_CLUSTER) cluster_forced = v;
@@ -315,50 +317,67 @@ class SimT final : public psim_sim {
     else allpairs_step_kernel<R, T, RI, MODE, false><<<grid, T, 0, stream>>>(a);
   }
 
-  // Tiling of the production all-pairs kernel: RI i-particles per lane (i-tile = 32 RI) and S
-  // blocks per cluster (j split).  The kernel keeps 4 blocks per SM resident, so the grid runs in
-  // waves of 4 x SMs blocks; power-of-two tilings of power-of-two N leave the last wave 14 % empty
-  // (1024 blocks on 592 slots).  Choose the pair that fills its last wave best, preferring more i
-  // per lane (better FMA : shared-memory ratio) and enough blocks to cover every SM.
-  void pick_tiling(int* ri_out, int* s_out) const {
-    const int64_t slots = (int64_t)sm_count * 4;
-    double best = -1.0;
-    int best_ri = 8, best_s = 1;
-    if (!ri_sel && !cluster_forced && blocks(i_hi - i_lo, 32 * 8) >= slots) {
-      // more than a wave of full-size tiles: measured, the block scheduler backfills well enough
-      *ri_out = 8; *s_out = 1;
-      return;
-    }
+  // Tiling of the production all-pairs kernel: RI i-particles per lane (i-tile = 32 RI), W warps
+  // per block and S blocks per cluster (the j range is split W x S ways).  Registers allow 16 warps
+  // per SM, i.e. 16/W blocks.  Small i-counts (one GPU at N = 65,536, or any sharded run) need the
+  // j split to fill the machine; the split costs little inside a block (shared-memory reduction)
+  // and more across a cluster (measured: clusters schedule less densely), so W grows first.
+  struct Tiling { int ri, w, s; };
+  Tiling pick_tiling() const {
+    Tiling best = {8, 4, 1};
+    if (!ri_sel && !cluster_forced && !warps_forced && blocks(i_hi - i_lo, 32 * 8) >= (int64_t)sm_count * 4)
+      return best;       // more than a wave of full-size tiles: the block scheduler backfills well enough
+    double best_eff = -1.0;
     for (int ri = 8; ri >= 6; --ri) {
       if (ri_sel && ri != ri_sel) continue;
       const int64_t itiles = blocks(i_hi - i_lo, 32 * ri);
-      for (int S = 1; S <= MAX_CLUSTER; ++S) {
-        if (cluster_forced && S != cluster_forced) continue;
-        const int64_t ctas = itiles * S;
-        const int64_t waves = (ctas + slots - 1) / slots;
-        double eff = (double)ctas / (double)(waves * slots);
-        eff *= 1.0 - 0.015 * (8 - ri);                       // fewer i per lane: a little less efficient
-        if (S > 1) eff *= 0.95 - 0.03 * (S - 1);            // measured: clusters schedule less densely, and more so the larger they are
-        if (ctas < slots / 2) eff *= 0.5;                    // leave no SM idle
-        if (eff > best) { best = eff; best_ri = ri; best_s = S; }
+      for (int w = 4; w <= 16; w *= 2) {
+        if (warps_forced && w != warps_forced) continue;
+        const int64_t slots = (int64_t)sm_count * (16 / w);
+        for (int S = 1; S <= MAX_CLUSTER; ++S) {
+          if (cluster_forced && S != cluster_forced) continue;
+          const int64_t ctas = itiles * S;
+          const int64_t waves = (ctas + slots - 1) / slots;
+          double eff = (double)ctas / (double)(waves * slots);
+          eff *= 1.0 - 0.015 * (8 - ri);                     // fewer i per lane: a little less efficient
+          if (w > 4) eff *= 0.99;
+          if (S > 1) eff *= 0.95 - 0.03 * (S - 1);           // measured cost of cluster scheduling
+          if (eff > best_eff) { best_eff = eff; best = {ri, w, S}; }
+        }
       }
     }
-    *ri_out = best_ri; *s_out = best_s;
+    return best;
   }
 
-  template <int MODE, int RIv>
+  template <int MODE, int RIv, int Wv>
   cudaError_t launch_cluster(const StepArgs<R>& a, int S, int64_t* grid_out) {
     const int64_t itiles = blocks(i_hi - i_lo, 32 * RIv);
+    auto kern = allpairs_warp_kernel<R, RIv, Wv, MODE>;
+    constexpr size_t smem = allpairs_warp_smem<R, RIv, Wv>();
+    static bool attr_set[64] = {false};
+    if (smem > 40 * 1024 && !attr_set[device & 63]) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      attr_set[device & 63] = true;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(itiles * S));
-    cfg.blockDim = dim3(T);
+    cfg.blockDim = dim3(32 * Wv);
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr;
     attr.id = cudaLaunchAttributeClusterDimension;
     attr.val.clusterDim.x = S; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
     cfg.attrs = &attr; cfg.numAttrs = 1;
     *grid_out = itiles * S;
-    return cudaLaunchKernelEx(&cfg, allpairs_warp_kernel<R, RIv, MODE>, a, S);
+    return cudaLaunchKernelEx(&cfg, kern, a, S);
+  }
+
+  template <int MODE, int RIv>
+  cudaError_t launch_cluster_w(const StepArgs<R>& a, int w, int S, int64_t* grid_out) {
+    if (w == 16) return launch_cluster<MODE, RIv, 16>(a, S, grid_out);
+    if (w == 8) return launch_cluster<MODE, RIv, 8>(a, S, grid_out);
+    return launch_cluster<MODE, RIv, 4>(a, S, grid_out);
   }
 
   template <int MODE>
@@ -368,11 +387,10 @@ class SimT final : public psim_sim {
       launch_v1<MODE>(a, *grid_out);
       return PSIM_OK;
     }
-    int ri = 8, S = 1;
-    pick_tiling(&ri, &S);
-    if (ri == 6) PSIM_CK((launch_cluster<MODE, 6>(a, S, grid_out)));
-    else if (ri == 7) PSIM_CK((launch_cluster<MODE, 7>(a, S, grid_out)));
-    else PSIM_CK((launch_cluster<MODE, 8>(a, S, grid_out)));
+    const Tiling t = pick_tiling();
+    if (t.ri == 6) PSIM_CK((launch_cluster_w<MODE, 6>(a, t.w, t.s, grid_out)));
+    else if (t.ri == 7) PSIM_CK((launch_cluster_w<MODE, 7>(a, t.w, t.s, grid_out)));
+    else PSIM_CK((launch_cluster_w<MODE, 8>(a, t.w, t.s, grid_out)));
     return PSIM_OK;
   }
 
