@@ -164,3 +164,28 @@ def test_generator_matches_reference_script_semantics():
     for n in (65536, 262144):
         ids, pos, vel, area = G.synthetic(n)
         assert len(ids) == n and pos.min() > 0 and (pos.max(0) < np.array(area)).all()
+
+
+def test_cli_tools_round_trip(tmp_path):
+    """tools/write_particle_file.py (seeded restatement of the reference generator) and
+    tools/check_output.py (headless play_simulation.py reader)."""
+    import sys
+    from conftest import ROOT
+    from particle_simulation_b200 import formats
+    dat = str(tmp_path / "b.dat")
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "write_particle_file.py"), "-o", dat, "-n", "3", "2", "2",
+           "-s", "10", "10", "10", "-vt", "0.1", "--seed", "7"]
+    subprocess.run(cmd, check=True, capture_output=True)
+    ids, pos, vel = formats.read_particles(dat)
+    assert len(ids) == 12 and (vel >= 0).all()
+    assert subprocess.run(cmd, capture_output=True).returncode != 0            # mode 'x': no overwrite
+    subprocess.run(cmd + ["-a"], check=True, capture_output=True)              # append restarts the ids
+    ids2, _, _ = formats.read_particles(dat)
+    assert list(ids2) == list(range(1, 13)) * 2
+    out = str(tmp_path / "t.output")
+    with formats.OutputWriter(out, (99.0, 99.0, 99.0)) as w:
+        w.write_frame(ids, pos, vel)
+        w.write_frame(ids, pos + 0.5, vel)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "check_output.py"), "-i", out, "--compare", out],
+                       capture_output=True, text=True)
+    assert r.returncode == 0 and "Number of blocks: 2 (header says 2)" in r.stdout and "max |dx| = 0" in r.stdout
