@@ -65,18 +65,22 @@ typedef struct psim_params {
 typedef enum psim_force_algo {
   PSIM_FORCE_ALL_PAIRS = 0,  /* tiled all-pairs scan, N(N-1) ordered pair tests per step */
   PSIM_FORCE_CELL_BINNED = 1 /* particles binned by LENGTH_OF_CELL, 27-cell neighbourhood
-                                (what module_particle_management.f08:52-108,179-339 achieves with lists) */
+                                (what module_particle_management.f08:52-108,179-339 achieves with lists);
+                                single-GPU and sharded handles */
 } psim_force_algo;
 
 typedef enum psim_option {
   PSIM_OPT_FORCE_ALGO = 0,      /* psim_force_algo */
   PSIM_OPT_FUSED_STEP = 1,      /* 1: force+kick+drift in one kernel (default), 0: separate kernels */
   PSIM_OPT_KERNEL_TIMING = 2,   /* 1: bracket every force-kernel launch with CUDA events */
-  PSIM_OPT_EXACT_DIFF_FILTER = 3 /* all-pairs kernel variant: 0 (default) cluster kernel with the
+  PSIM_OPT_EXACT_DIFF_FILTER = 3, /* all-pairs kernel variant: 0 (default) warp-autonomous kernel with the
                                     norm-expansion pre-filter (3 FMAs per ordered pair); 1 first-generation
                                     kernel with the distance test in difference form (3 sub, 1 mul, 2 FMA,
                                     1 compare per pair: the literal reading of stoermer:117-121);
                                     2 first-generation kernel with the pre-filter */
+  PSIM_OPT_CELLS_INDEXED = 4     /* 1: on a single-GPU handle use the cell-binned variant of sharded runs
+                                    (state stays in particle order, cell-ordered copy of the positions);
+                                    sharded handles always use it.  Set before the cell path is first used. */
 } psim_option;
 
 typedef struct psim_counters {

@@ -153,6 +153,7 @@ class SimT final : public psim_sim {
   int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
   int warps_forced = 0;
+  bool cells_indexed = false;   // single GPU: use the sharded runs' index-based cell path (tests)
   int sm_count = 148;
 
   int device = 0;
@@ -355,7 +356,7 @@ class SimT final : public psim_sim {
     auto kern = allpairs_warp_kernel<R, RIv, Wv, MODE>;
     constexpr size_t smem = allpairs_warp_smem<R, RIv, Wv>();
     static bool attr_set[64] = {false};
-    if (smem > 40 * 1024 && !attr_set[device & 63]) {
+    if (!attr_set[device & 63]) {   // static tiles + dynamic accumulators can exceed the 48 KB default
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
       attr_set[device & 63] = true;
@@ -583,12 +584,11 @@ class SimT final : public psim_sim {
     switch (opt) {
       case PSIM_OPT_FORCE_ALGO:
         if (value != PSIM_FORCE_ALL_PAIRS && value != PSIM_FORCE_CELL_BINNED) return PSIM_ERR_INVALID_ARGUMENT;
-        if (value == PSIM_FORCE_CELL_BINNED && world > 1) {
-          g_last_error = "cell-binned force is single-GPU in this version";
-          return PSIM_ERR_UNSUPPORTED;
-        }
         algo = (int)value; cells.invalidate(); return PSIM_OK;
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
+      case PSIM_OPT_CELLS_INDEXED:
+        if (cells.allocated()) { g_last_error = "PSIM_OPT_CELLS_INDEXED must be set before the cell path is first used"; return PSIM_ERR_INVALID_ARGUMENT; }
+        cells_indexed = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER:
         if (value < 0 || value > 2) return PSIM_ERR_INVALID_ARGUMENT;

@@ -167,25 +167,40 @@ __global__ void iota_kernel(int32_t* p, int64_t n) {
 // dense for a divergent exact evaluation per hit, cheap enough to queue.
 // Phase 2 walks the queue with the exact pair term in the working precision.
 // Sums run in ascending slot order: deterministic.
-template <class R, int MODE, int QCAP, int T>
+//
+// INDEXED = false: the state itself is in cell order (single GPU): slot k holds
+// particle k of the permuted arrays and posj is a.pos_cur.
+// INDEXED = true (sharded runs): the state stays in particle order; posj is a
+// cell-ordered COPY of all positions, perm maps slot -> particle, and the block
+// walks own_slots, the cell-ordered list of the slots whose particle this rank
+// owns.  The force sum uses slots, the kick/drift epilogue the particle index.
+template <class R, int MODE, int QCAP, int T, bool INDEXED>
 __global__ void __launch_bounds__(T)
-cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
-                  const int32_t* __restrict__ cell_start, int ncell, int64_t n) {
+cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const int32_t* __restrict__ cell_of,
+                  const int32_t* __restrict__ cell_start, const int32_t* __restrict__ own_slots,
+                  const int32_t* __restrict__ own_start, const int32_t* __restrict__ perm, int ncell, int64_t n) {
   constexpr int W = T / 32, TJ = 32;
   __shared__ int32_t queue[QCAP * T];
   __shared__ __align__(16) float tx[W][2][TJ], ty[W][2][TJ], tz[W][2][TJ], tw[W][2][TJ];
   const Consts<R>& c = a.c;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t k = (int64_t)blockIdx.x * T + tid;
+  const int64_t idx = (int64_t)blockIdx.x * T + tid;
+  int64_t k = -1;              // slot in cell order (j-side numbering)
+  int64_t ip = -1;             // particle index in the state arrays (epilogue numbering)
+  if (INDEXED) {
+    if (idx < own_start[ncell]) { k = own_slots[idx]; ip = perm[k]; }
+  } else if (idx < n) {
+    k = idx; ip = idx;
+  }
   const float rcut = (float)c.r_cut;
   const float cut2f = (float)c.cut2_pad * (1.0f + 1.0e-6f);
 
   R xi = 0, yi = 0, zi = 0, fx = 0, fy = 0, fz = 0;
   float fxi = 0.f, fyi = 0.f, fzi = 0.f, cutf = -1.0e30f;
   int cell = ncell;
-  if (k < n) {
+  if (k >= 0) {
     cell = cell_of[k];
-    const Real4<R> p = a.pos_cur[k];
+    const Real4<R> p = posj[k];
     if (cell < ncell && !(p.w >= c.huge)) {
       xi = p.x; yi = p.y; zi = p.z;
       const FilterRec f = filter_record(p, c, rcut);
@@ -209,13 +224,13 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
     if (cnt == 0) return;
     // software pipeline: the next two records are in flight while two pair terms are evaluated
     int ja = queue[tid], jb = cnt > 1 ? queue[T + tid] : ja;
-    Real4<R> qa = a.pos_cur[ja], qb = a.pos_cur[jb];
+    Real4<R> qa = posj[ja], qb = posj[jb];
     int e = 0;
     for (; e + 1 < cnt; e += 2) {
       const int j0 = ja, j1 = jb;
       const Real4<R> q0 = qa, q1 = qb;
-      if (e + 2 < cnt) { ja = queue[(e + 2) * T + tid]; qa = a.pos_cur[ja]; }
-      if (e + 3 < cnt) { jb = queue[(e + 3) * T + tid]; qb = a.pos_cur[jb]; }
+      if (e + 2 < cnt) { ja = queue[(e + 2) * T + tid]; qa = posj[ja]; }
+      if (e + 3 < cnt) { jb = queue[(e + 3) * T + tid]; qb = posj[jb]; }
       R ax0 = (R)0, ay0 = (R)0, az0 = (R)0, ax1 = (R)0, ay1 = (R)0, az1 = (R)0;
       if (j0 != (int)k) pair_force(xi, yi, zi, q0.x, q0.y, q0.z, c, ax0, ay0, az0);
       if (j1 != (int)k) pair_force(xi, yi, zi, q1.x, q1.y, q1.z, c, ax1, ay1, az1);
@@ -230,7 +245,7 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
     const int nx = c.nc[0], ny = c.nc[1];
     auto fetch = [&](int j, int tb) {      // global load only: the conversion waits until the data is needed
       Real4<R> p; p.x = p.y = p.z = (R)0; p.w = c.huge;
-      if (j < tb) p = a.pos_cur[j];
+      if (j < tb) p = posj[j];
       return p;
     };
     auto stage = [&](int buf, const Real4<R>& p) {
@@ -292,8 +307,85 @@ cell_force_kernel(const StepArgs<R> a, const int32_t* __restrict__ cell_of,
   }
 
   R first = (R)0, second = (R)0;
-  if (k < n) step_epilogue<R, MODE>(a, k, fx, fy, fz, first, second);
+  if (ip >= 0) step_epilogue<R, MODE>(a, ip, fx, fy, fz, first, second);
   if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part);
+}
+
+// ---- sharded runs: binning by index, state stays in particle order ------------
+
+// S1: cell of every PARTICLE (inactive -> tail bucket) + histograms of all and of owned particles.
+template <class R, int T>
+__global__ void __launch_bounds__(T)
+cellsx_key_kernel(const Real4<R>* __restrict__ pos, int32_t* __restrict__ key, unsigned* __restrict__ count,
+                  unsigned* __restrict__ own_count, int64_t n, int64_t i_lo, int64_t i_hi, int ncell, Consts<R> c,
+                  const int* flag, int force) {
+  if (!force && !*flag) return;
+  const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
+  if (i >= n) return;
+  const Real4<R> p = pos[i];
+  int cell = ncell;
+  if (!(p.w >= c.huge)) {
+    const int cx = clamp_cell(p.x, c.cell[0], c.nc[0]);
+    const int cy = clamp_cell(p.y, c.cell[1], c.nc[1]);
+    const int cz = clamp_cell(p.z, c.cell[2], c.nc[2]);
+    cell = (cx - 1) + c.nc[0] * ((cy - 1) + c.nc[1] * (cz - 1));
+  }
+  key[i] = cell;
+  atomicAdd(&count[cell], 1u);
+  if (i >= i_lo && i < i_hi && cell < ncell) atomicAdd(&own_count[cell], 1u);
+}
+
+// S4: per cell, put the slot -> particle map in ascending particle order (deterministic),
+// record the cell of every slot, and list the slots of the owned particles in cell order.
+template <int T>
+__global__ void __launch_bounds__(T)
+cellsx_order_kernel(const int32_t* __restrict__ cell_start, const int32_t* __restrict__ own_start,
+                    int32_t* __restrict__ perm, int32_t* __restrict__ cell_of, int32_t* __restrict__ own_slots,
+                    unsigned* __restrict__ count, unsigned* __restrict__ own_count, int64_t i_lo, int64_t i_hi,
+                    int ncell, const int* flag, int force) {
+  if (!force && !*flag) return;
+  const int cell = blockIdx.x * T + threadIdx.x;
+  if (cell > ncell) return;
+  count[cell] = 0u;
+  own_count[cell] = 0u;
+  const int lo = cell_start[cell], hi = cell_start[cell + 1];
+  if (cell == ncell) {                     // inactive tail: never read through the cell tables
+    for (int a = lo; a < hi; ++a) cell_of[a] = ncell;
+    return;
+  }
+  for (int a = lo + 1; a < hi; ++a) {
+    const int32_t v = perm[a];
+    int b = a - 1;
+    while (b >= lo && perm[b] > v) { perm[b + 1] = perm[b]; --b; }
+    perm[b + 1] = v;
+  }
+  int m = own_start[cell];
+  for (int a = lo; a < hi; ++a) {
+    cell_of[a] = cell;
+    const int32_t i = perm[a];
+    if (i >= i_lo && i < i_hi) own_slots[m++] = a;
+  }
+}
+
+// every step: the cell-ordered copy of all positions
+template <class R, int T>
+__global__ void __launch_bounds__(T)
+cellsx_gather_kernel(Real4<R>* __restrict__ posj, const Real4<R>* __restrict__ pos,
+                     const int32_t* __restrict__ perm, int64_t n) {
+  const int64_t k = (int64_t)blockIdx.x * T + threadIdx.x;
+  if (k < n) posj[k] = pos[perm[k]];
+}
+
+// every fused step of a sharded run: owned INACTIVE particles are not in own_slots, so their
+// (frozen) record is carried into the next position buffer here
+template <class R, int T>
+__global__ void __launch_bounds__(T)
+cellsx_carry_inactive_kernel(const Real4<R>* __restrict__ pos_cur, Real4<R>* __restrict__ pos_nxt,
+                             int64_t i_lo, int64_t i_hi, Consts<R> c) {
+  const int64_t i = i_lo + (int64_t)blockIdx.x * T + threadIdx.x;
+  if (i >= i_hi) return;
+  const Real4<R> p = pos_cur[i];
+  if (p.w >= c.huge) pos_nxt[i] = p;
 }
 
 template <class R>
@@ -309,16 +401,23 @@ struct CellPath {
   unsigned *count = nullptr, *fill = nullptr;
   int32_t *orig = nullptr, *cell_of = nullptr;
   CellArrays<R> spare = {};
+  // indexed (sharded) mode: state stays in particle order
+  bool indexed = false;
+  Real4<R>* posj = nullptr;
+  int32_t *own_slots = nullptr, *own_start = nullptr;
+  unsigned* own_count = nullptr;
 
-  bool allocated() const { return orig != nullptr; }
-  const int32_t* orig_or_null() const { return orig; }
+  bool allocated() const { return key != nullptr; }
+  const int32_t* orig_or_null() const { return indexed ? nullptr : orig; }
 
   void destroy() {
     cudaFree(key); cudaFree(src); cudaFree(cell_start); cudaFree(count); cudaFree(fill);
     cudaFree(orig); cudaFree(cell_of);
     for (int q = 0; q < 5; ++q) cudaFree(spare.a[q]);
     cudaFree(spare.orig); cudaFree(spare.cell_of);
+    cudaFree(posj); cudaFree(own_slots); cudaFree(own_start); cudaFree(own_count);
     key = src = cell_start = nullptr; count = fill = nullptr; orig = cell_of = nullptr;
+    posj = nullptr; own_slots = own_start = nullptr; own_count = nullptr;
     spare = CellArrays<R>();
     binned = false;
   }
@@ -331,8 +430,25 @@ struct CellPath {
     if (allocated()) return cudaSuccess;
     n = sim.n; n_pad = sim.n_pad;
     ncell = sim.c.nc[0] * sim.c.nc[1] * sim.c.nc[2];
+    indexed = sim.world > 1 || sim.cells_indexed;
     cudaError_t e;
 #define PSIM_TRY(x) if ((e = (x)) != cudaSuccess) return e
+    if (indexed) {
+      PSIM_TRY(cudaMalloc(&key, sizeof(int32_t) * n_pad));
+      PSIM_TRY(cudaMalloc(&src, sizeof(int32_t) * n_pad));            // perm: slot -> particle
+      PSIM_TRY(cudaMalloc(&cell_start, sizeof(int32_t) * (ncell + 2)));
+      PSIM_TRY(cudaMalloc(&own_start, sizeof(int32_t) * (ncell + 2)));
+      PSIM_TRY(cudaMalloc(&count, sizeof(unsigned) * (ncell + 1)));
+      PSIM_TRY(cudaMalloc(&own_count, sizeof(unsigned) * (ncell + 1)));
+      PSIM_TRY(cudaMalloc(&fill, sizeof(unsigned) * (ncell + 1)));
+      PSIM_TRY(cudaMalloc(&cell_of, sizeof(int32_t) * n_pad));
+      PSIM_TRY(cudaMalloc(&own_slots, sizeof(int32_t) * n_pad));
+      PSIM_TRY(cudaMalloc(&posj, sizeof(Real4<R>) * n_pad));
+      PSIM_TRY(cudaMemsetAsync(count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
+      PSIM_TRY(cudaMemsetAsync(own_count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
+      binned = false;
+      return cudaSuccess;
+    }
     PSIM_TRY(cudaMalloc(&key, sizeof(int32_t) * n_pad));
     PSIM_TRY(cudaMalloc(&src, sizeof(int32_t) * n_pad));
     PSIM_TRY(cudaMalloc(&cell_start, sizeof(int32_t) * (ncell + 2)));
@@ -360,6 +476,17 @@ struct CellPath {
     const int f = force ? 1 : 0;
     const unsigned gn = (unsigned)((n + T - 1) / T);
     cudaStream_t st = sim.stream;
+    if (indexed) {
+      cellsx_key_kernel<R, T><<<gn, T, 0, st>>>(posbuf, key, count, own_count, n, sim.i_lo, sim.i_hi, ncell, sim.c, flag, f);
+      cells_scan_kernel<<<1, 1024, 0, st>>>(count, cell_start, fill, ncell + 1, flag, f);
+      cells_scan_kernel<<<1, 1024, 0, st>>>(own_count, own_start, fill, ncell + 1, flag, f);
+      cells_scatter_kernel<T><<<gn, T, 0, st>>>(key, cell_start, fill, src, n, flag, f);
+      cellsx_order_kernel<T><<<(unsigned)((ncell + 1 + T - 1) / T), T, 0, st>>>(
+          cell_start, own_start, src, cell_of, own_slots, count, own_count, sim.i_lo, sim.i_hi, ncell, flag, f);
+      launches += 5;
+      if (force) binned = true;
+      return;
+    }
     cells_key_kernel<R, T><<<gn, T, 0, st>>>(posbuf, key, count, n, ncell, sim.c, flag, f);
     cells_scan_kernel<<<1, 1024, 0, st>>>(count, cell_start, fill, ncell + 1, flag, f);
     cells_scatter_kernel<T><<<gn, T, 0, st>>>(key, cell_start, fill, src, n, flag, f);
@@ -378,13 +505,39 @@ struct CellPath {
     if (ensure(sim) != cudaSuccess) return PSIM_ERR_CUDA;
     if (!binned) rebin(sim, sim.pos[sim.cur], 0, true);
     const StepArgs<R> a = sim.step_args();
+    if (indexed) {
+      const int64_t n_own = sim.i_hi - sim.i_lo;
+      if (n_own <= 0) { if (mode == MODE_FORCE_KICK_DRIFT) sim.top2_count = 0; return PSIM_OK; }
+      const unsigned gn = (unsigned)((n + T - 1) / T);
+      cellsx_gather_kernel<R, T><<<gn, T, 0, sim.stream>>>(posj, a.pos_cur, src, n);
+      const unsigned grid = (unsigned)((n_own + TF - 1) / TF);
+      if (mode == MODE_FORCE)
+        cell_force_kernel<R, MODE_FORCE, QCAP, TF, true><<<grid, TF, 0, sim.stream>>>(
+            a, posj, cell_of, cell_start, own_slots, own_start, src, ncell, n);
+      else if (mode == MODE_FORCE_KICK)
+        cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF, true><<<grid, TF, 0, sim.stream>>>(
+            a, posj, cell_of, cell_start, own_slots, own_start, src, ncell, n);
+      else {
+        cellsx_carry_inactive_kernel<R, T><<<(unsigned)((n_own + T - 1) / T), T, 0, sim.stream>>>(
+            a.pos_cur, a.pos_nxt, sim.i_lo, sim.i_hi, sim.c);
+        cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF, true><<<grid, TF, 0, sim.stream>>>(
+            a, posj, cell_of, cell_start, own_slots, own_start, src, ncell, n);
+        sim.top2_count = grid;
+        ++launches;
+      }
+      launches += 2;
+      return PSIM_OK;
+    }
     const unsigned grid = (unsigned)((n + TF - 1) / TF);
     if (mode == MODE_FORCE)
-      cell_force_kernel<R, MODE_FORCE, QCAP, TF><<<grid, TF, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
+      cell_force_kernel<R, MODE_FORCE, QCAP, TF, false><<<grid, TF, 0, sim.stream>>>(
+          a, a.pos_cur, cell_of, cell_start, nullptr, nullptr, nullptr, ncell, n);
     else if (mode == MODE_FORCE_KICK)
-      cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF><<<grid, TF, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
+      cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF, false><<<grid, TF, 0, sim.stream>>>(
+          a, a.pos_cur, cell_of, cell_start, nullptr, nullptr, nullptr, ncell, n);
     else {
-      cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF><<<grid, TF, 0, sim.stream>>>(a, cell_of, cell_start, ncell, n);
+      cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF, false><<<grid, TF, 0, sim.stream>>>(
+          a, a.pos_cur, cell_of, cell_start, nullptr, nullptr, nullptr, ncell, n);
       sim.top2_count = grid;
     }
     ++launches;

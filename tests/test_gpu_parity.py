@@ -26,15 +26,19 @@ def _ref_files():
     return os.path.join(GOLDEN, "two_cubes_432.dat")
 
 
-ALGOS = ["allpairs", "cells"]
+# cells_indexed: the cell-binned variant sharded runs use (state in particle order, cell-ordered
+# copy of the positions, index list of the owned particles), exercised here on one GPU
+ALGOS = ["allpairs", "cells", "cells_indexed"]
 
 
 def _select(psim, sim, algo):
-    sim.set_option(psim.OPT_FORCE_ALGO, psim.FORCE_CELL_BINNED if algo == "cells" else psim.FORCE_ALL_PAIRS)
+    if algo == "cells_indexed":
+        sim.set_option(psim.OPT_CELLS_INDEXED, 1)
+    sim.set_option(psim.OPT_FORCE_ALGO, psim.FORCE_ALL_PAIRS if algo == "allpairs" else psim.FORCE_CELL_BINNED)
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "cells"])
+@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "cells", "cells_indexed"])
 def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     ids, pos, vel = two_cubes()
     p = psim.make_params()
@@ -45,8 +49,11 @@ def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     if variant == "allpairs_exact_diff":
         sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 1)
         sim.set_positions(pos)
-    elif variant == "cells":
-        _select(psim, sim, "cells")
+    elif variant == "allpairs_v1_filter":
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 2)
+        sim.set_positions(pos)
+    elif variant.startswith("cells"):
+        _select(psim, sim, variant)
         sim.set_positions(pos)
     f = sim.forces()
     scale = np.abs(f_ref).max()

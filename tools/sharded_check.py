@@ -33,7 +33,7 @@ def main():
         return bytes(buf.cpu().numpy().tobytes())
 
     ok = True
-    for precision, xtol in ((8, 1e-9), (4, 2e-4)):
+    for precision, xtol, algo in ((8, 1e-9, "allpairs"), (4, 2e-4, "allpairs"), (8, 1e-9, "cells"), (4, 2e-4, "cells")):
         for scenario in ("calm", "leaving"):
             if scenario == "calm":
                 ids, pos, vel = two_cubes()
@@ -45,6 +45,8 @@ def main():
             sim = P.Simulation(P.make_params(**kw), ids, pos, vel, precision, device=local, rank=rank, world=world,
                                nccl_unique_id=fresh_uid())
             assert (sim.i_lo, sim.i_hi) == sharding.shard_bounds(n, rank, world)
+            if algo == "cells":
+                sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
             o = O.Oracle(O.make_params(**kw), precision, ids, pos, vel)
             for chunk in (1, 30, 29):
                 sim.advance(chunk); o.advance(chunk)
@@ -67,8 +69,8 @@ def main():
                 ix = np.unravel_index(np.abs(x - xr).argmax(), x.shape); iv = np.unravel_index(np.abs(vm - vr).argmax(), vm.shape)
                 print("rank %d detail: x[%s]=%r ref %r act %d/%d | v[%s]=%r ref %r act %d/%d flags_equal=%s" % (
                     rank, ix, x[ix], xr[ix], a[ix[0]], ar[ix[0]], iv, vm[iv], vr[iv], a[iv[0]], ar[iv[0]], np.array_equal(a, ar)), flush=True)
-                print("rank %d: MISMATCH precision=%d scenario=%s dx=%g dv=%g rebuilds %d vs %d" % (
-                    rank, precision, scenario, np.abs(x - xr).max(), np.abs(vm - vr).max(),
+                print("rank %d: MISMATCH algo=%s precision=%d scenario=%s dx=%g dv=%g rebuilds %d vs %d" % (
+                    rank, algo, precision, scenario, np.abs(x - xr).max(), np.abs(vm - vr).max(),
                     sim.counters().rebuilds, o.rebuilds))
             ok = ok and good
             sim.close(); o.close()
