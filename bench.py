@@ -353,18 +353,28 @@ def main():
         "roofline": roofline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }
 
-    if world == 1 and args.algo == "allpairs" and not args.no_cells:
+    if args.algo == "allpairs" and not args.no_cells:
         # the same job through the cell-binned path: what a user who wants
-        # timesteps/s would select; single GPU in this version
-        cs = P.Simulation(params, ids, pos, vel, prec, device=local_rank)
+        # timesteps/s selects.  Sharded runs keep ownership by particle index and all-gather the
+        # positions per step exactly like the all-pairs path.
+        uid2 = None
+        if world > 1:
+            buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                buf.copy_(torch.frombuffer(bytearray(native.comm_unique_id()), dtype=torch.uint8))
+            dist.broadcast(buf, 0)
+            uid2 = bytes(buf.cpu().numpy().tobytes())
+        cs = P.Simulation(params, ids, pos, vel, prec, device=local_rank, rank=rank, world=world, nccl_unique_id=uid2)
         cs.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
         cs.advance(30)
         csteps = max(args.steps, 200)
-        cms = cs.advance_timed(csteps)
+        barrier()
+        cms = max_over_ranks(cs.advance_timed(csteps))
+        barrier()
         cc = cs.counters()
         line["cell_binned"] = {"timesteps_per_s": csteps / (cms * 1e-3), "ms_per_step": cms / csteps,
                                "value": pairs_total * csteps / (cms * 1e-3), "unit": "pair-interactions/s",
-                               "steps": csteps, "rebuilds": int(cc.rebuilds),
+                               "steps": csteps, "rebuilds": int(cc.rebuilds), "n_gpus": world,
                                "note": "equivalent rate: N(N-1) x timesteps/s; the path tests only the 27-cell "
                                        "neighbourhood of each particle"}
         cs.close()

@@ -78,9 +78,6 @@ typedef enum psim_option {
                                     kernel with the distance test in difference form (3 sub, 1 mul, 2 FMA,
                                     1 compare per pair: the literal reading of stoermer:117-121);
                                     2 first-generation kernel with the pre-filter */
-  PSIM_OPT_CELLS_INDEXED = 4     /* 1: on a single-GPU handle use the cell-binned variant of sharded runs
-                                    (state stays in particle order, cell-ordered copy of the positions);
-                                    sharded handles always use it.  Set before the cell path is first used. */
 } psim_option;
 
 typedef struct psim_counters {

@@ -31,7 +31,9 @@ struct StepArgs {
   Real4<R>* f_old;
   Real4<R>* f_new;
   Real4<R>* disp;
-  R* top2_part;              // [2 * gridDim.x] per-block two largest |disp|
+  R* top2_part;              // [2 * gridDim.x] per-block two largest |disp| (scratch)
+  R* rank_pair;              // [2] this rank's two largest |disp|, written by the block that finishes last
+  unsigned* ticket;          // block counter of that hand-over (0 between launches)
   int64_t n_pad;             // multiple of the j-tile
   int64_t i_lo, i_hi;        // owned slice of i (multi-GPU shard); i_hi <= n
   Consts<R> c;
@@ -56,9 +58,13 @@ __device__ __forceinline__ R drift_one(const Consts<R>& c, Real4<R> x, const Rea
   return dr;
 }
 
+// Block-level two largest values -> part[blockIdx.x]; the block that finishes
+// last merges every block's pair into rank_pair (threadfence + ticket), so the
+// rebuild trigger needs no reduction kernel of its own.
 template <class R, int T>
-__device__ __forceinline__ void block_top2_store(R first, R second, R* part) {
+__device__ __forceinline__ void block_top2_store(R first, R second, R* part, unsigned* ticket, R* rank_pair) {
   __shared__ R s_first[T / 32], s_second[T / 32];
+  __shared__ bool s_last;
   top2_warp_reduce(first, second);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) { s_first[warp] = first; s_second[warp] = second; }
@@ -67,7 +73,30 @@ __device__ __forceinline__ void block_top2_store(R first, R second, R* part) {
     first = lane < T / 32 ? s_first[lane] : (R)0;
     second = lane < T / 32 ? s_second[lane] : (R)0;
     top2_warp_reduce(first, second);
-    if (lane == 0) { part[2 * blockIdx.x] = first; part[2 * blockIdx.x + 1] = second; }
+    if (lane == 0) {
+      part[2 * blockIdx.x] = first; part[2 * blockIdx.x + 1] = second;
+      __threadfence();
+      s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  first = second = (R)0;
+  const volatile R* vp = part;
+  for (unsigned b = threadIdx.x; b < gridDim.x; b += T) {
+    top2_push(first, second, vp[2 * b]);
+    top2_push(first, second, vp[2 * b + 1]);
+  }
+  top2_warp_reduce(first, second);
+  __syncthreads();
+  if (lane == 0) { s_first[warp] = first; s_second[warp] = second; }
+  __syncthreads();
+  if (warp == 0) {
+    first = lane < T / 32 ? s_first[lane] : (R)0;
+    second = lane < T / 32 ? s_second[lane] : (R)0;
+    top2_warp_reduce(first, second);
+    if (lane == 0) { rank_pair[0] = first; rank_pair[1] = second; *ticket = 0u; }
   }
 }
 
@@ -196,7 +225,7 @@ allpairs_step_kernel(const StepArgs<R> a) {
 #pragma unroll
   for (int r = 0; r < RI; ++r)
     if (ig[r] >= 0) step_epilogue<R, MODE>(a, ig[r], fx[r], fy[r], fz[r], first, second);
-  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part);
+  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part, a.ticket, a.rank_pair);
 }
 
 // Ordered in-range pair count with the exact predicate (P_in).

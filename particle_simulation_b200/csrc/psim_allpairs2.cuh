@@ -226,7 +226,7 @@ allpairs_warp_kernel(const StepArgs<R> a, const int S) {
     if (i < a.i_hi) step_epilogue<R, MODE>(a, i, sx, sy, sz, first, second);
   }
   cluster.sync();                            // nobody leaves while its shared memory is still being read
-  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part);
+  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part, a.ticket, a.rank_pair);
 }
 
 }  // namespace psim

@@ -153,7 +153,6 @@ class SimT final : public psim_sim {
   int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
   int warps_forced = 0;
-  bool cells_indexed = false;   // single GPU: use the sharded runs' index-based cell path (tests)
   int sm_count = 148;
 
   int device = 0;
@@ -166,7 +165,7 @@ class SimT final : public psim_sim {
   int cur = 0;
   Real4<R>*vel = nullptr, *f_old = nullptr, *f_new = nullptr, *disp = nullptr;
   R* top2_part = nullptr;
-  int64_t top2_cap = 0, top2_count = 0;
+  int64_t top2_cap = 0;
   R* top2_rank = nullptr;       // [2 * world]
   Control* ctrl = nullptr;
   int parity = 0;
@@ -307,6 +306,8 @@ class SimT final : public psim_sim {
     a.pos_cur = pos[cur]; a.pos_nxt = pos[cur ^ 1];
     a.vel = vel; a.f_old = f_old; a.f_new = f_new; a.disp = disp;
     a.top2_part = top2_part;
+    a.rank_pair = top2_rank + 2 * rank;
+    a.ticket = &ctrl->ticket;
     a.n_pad = n_pad; a.i_lo = i_lo; a.i_hi = i_hi;
     a.c = c;
     return a;
@@ -419,7 +420,7 @@ class SimT final : public psim_sim {
       psim_status st;
       if (mode == MODE_FORCE) st = launch_allpairs<MODE_FORCE>(a, &grid);
       else if (mode == MODE_FORCE_KICK) st = launch_allpairs<MODE_FORCE_KICK>(a, &grid);
-      else { st = launch_allpairs<MODE_FORCE_KICK_DRIFT>(a, &grid); top2_count = grid; }
+      else st = launch_allpairs<MODE_FORCE_KICK_DRIFT>(a, &grid);
       if (st != PSIM_OK) return st;
       ++launches;
     }
@@ -439,30 +440,51 @@ class SimT final : public psim_sim {
     return PSIM_OK;
   }
 
-  // After x_{n+1} of the owned slice is in pos[cur^1]: exchange (sharded),
-  // evaluate the rebuild trigger, apply the rebuild's side effects, swap.
+  // One cooperative launch: trigger, rebuild side effects, (cell path) re-binning and the
+  // cell-ordered position copy.  pos_new is the buffer that is current from here on.
+  int house_grid_max = 0;
+  psim_status launch_housekeeping(Real4<R>* pos_new, Real4<R>* pos_other, bool with_trigger, bool force_rebin,
+                                  bool flag_in_ctrl = false) {
+    if (!house_grid_max) {
+      int per_sm = 0;
+      PSIM_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, housekeeping_kernel<R>, 256, 0));
+      house_grid_max = std::max(1, per_sm) * sm_count;
+    }
+    HouseArgs<R> h = {};
+    h.pos_new = pos_new; h.pos_other = pos_other; h.disp = disp;
+    h.rank_pairs = with_trigger ? top2_rank : nullptr;
+    h.world = world; h.flag_in_ctrl = flag_in_ctrl ? 1 : 0;
+    h.ctrl = ctrl; h.parity = parity;
+    h.n = n; h.i_lo = i_lo; h.i_hi = i_hi; h.c = c;
+    h.cells = (algo == PSIM_FORCE_CELL_BINNED && cells.allocated()) ? 1 : 0;
+    h.force_rebin = force_rebin ? 1 : 0;
+    if (h.cells) cells.fill_args(h);
+    const int grid = (int)std::min<int64_t>(house_grid_max, std::max<int64_t>(2, blocks(n, 256)));
+    void* args[] = {&h};
+    PSIM_CK(cudaLaunchCooperativeKernel((const void*)housekeeping_kernel<R>, dim3(grid), dim3(256), args, 0, stream));
+    ++launches;
+    if (h.cells && (force_rebin || cells.binned)) cells.binned = true;
+    return PSIM_OK;
+  }
+
+  // After x_{n+1} of the owned slice is in pos[cur^1]: exchange (sharded), then housekeeping, swap.
   psim_status finish_drift() {
     Real4<R>* nxt = pos[cur ^ 1];
+    if (i_hi <= i_lo) PSIM_CK(cudaMemsetAsync(top2_rank + 2 * rank, 0, 2 * sizeof(R), stream));   // nothing owned
+    bool flag_in_ctrl = false;
     if (world > 1) {
-      top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_part, top2_count, top2_rank + 2 * rank, ctrl, parity, c);
-      ++launches;
       PSIM_NCCL(g_nccl.GroupStart());
       PSIM_NCCL(g_nccl.AllGather(nxt + shard * rank, nxt, (size_t)shard * 4, NcclType<R>::v, comm, stream));
       PSIM_NCCL(g_nccl.AllGather(top2_rank + 2 * rank, top2_rank, 2, NcclType<R>::v, comm, stream));
       PSIM_NCCL(g_nccl.GroupEnd());
-      top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_rank, world, nullptr, ctrl, parity, c);
-      ++launches;
     } else if (c.slices > 1) {
-      slice_trigger_kernel<R><<<c.slices, 256, 0, stream>>>(nxt, disp, cells.orig_or_null(), n, ctrl, parity, c);
+      // NB_OF_THREADS > 1: the reference's per-slice trigger (single GPU)
+      slice_trigger_kernel<R><<<c.slices, 256, 0, stream>>>(nxt, disp, nullptr, n, ctrl, parity, c);
       ++launches;
-    } else {
-      top2_merge_kernel<R><<<1, 256, 0, stream>>>(top2_part, top2_count, nullptr, ctrl, parity, c);
-      ++launches;
+      flag_in_ctrl = true;
     }
-    rebuild_effects_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nxt, disp, n, i_lo, i_hi, ctrl, parity, c);
-    ++launches;
-    // cell path: re-order the state by cell when (and only when) the trigger fired
-    if (algo == PSIM_FORCE_CELL_BINNED && cells.allocated()) cells.rebin(*this, nxt, parity, false);
+    psim_status st = launch_housekeeping(nxt, pos[cur], true, false, flag_in_ctrl);
+    if (st != PSIM_OK) return st;
     parity ^= 1;
     cur ^= 1;
     return PSIM_OK;
@@ -477,9 +499,9 @@ class SimT final : public psim_sim {
         if (i_hi > i_lo) {
           const int64_t grid = blocks(i_hi - i_lo, TS);
           drift_kernel<R, TS><<<grid, TS, 0, stream>>>(pos[cur], pos[cur ^ 1], vel, f_old, f_new, disp, top2_part,
-                                                       i_lo, i_hi, c);
-          top2_count = grid; ++launches;
-        } else top2_count = 0;
+                                                       &ctrl->ticket, top2_rank + 2 * rank, i_lo, i_hi, c);
+          ++launches;
+        }
       }
       pending_drift = false;
       psim_status st = finish_drift();
@@ -489,7 +511,6 @@ class SimT final : public psim_sim {
         st = launch_force(last ? MODE_FORCE_KICK : MODE_FORCE_KICK_DRIFT);
         if (st != PSIM_OK) return st;
         pending_drift = !last && (i_hi > i_lo);
-        if (!last && i_hi <= i_lo) top2_count = 0;
       } else {
         st = launch_force(MODE_FORCE);
         if (st != PSIM_OK) return st;
@@ -586,9 +607,6 @@ class SimT final : public psim_sim {
         if (value != PSIM_FORCE_ALL_PAIRS && value != PSIM_FORCE_CELL_BINNED) return PSIM_ERR_INVALID_ARGUMENT;
         algo = (int)value; cells.invalidate(); return PSIM_OK;
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
-      case PSIM_OPT_CELLS_INDEXED:
-        if (cells.allocated()) { g_last_error = "PSIM_OPT_CELLS_INDEXED must be set before the cell path is first used"; return PSIM_ERR_INVALID_ARGUMENT; }
-        cells_indexed = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER:
         if (value < 0 || value > 2) return PSIM_ERR_INVALID_ARGUMENT;

@@ -1,22 +1,30 @@
-// psim_cells.cuh — cell-binned force path.
+// psim_cells.cuh — cell-binned force path and the per-step
+// housekeeping kernel.
 //
 // What the reference achieves with linked cells and per-particle neighbour
 // lists (module_particle_management.f08:52-108, 128-137, 179-339), done the GPU
-// way: whenever the reference would rebuild its lists (the displacement trigger
-// of module_stoermer_verlet_method.f08:177-185 fired), the particle STATE is
-// physically re-ordered by cell (x fastest, the reference's own grid:
-// nint(area/cell) cells, index ceiling(x/cell), pm:62, 95), so that the 27-cell
-// neighbourhood of a particle is nine contiguous runs of slots.  Between
-// rebuilds the order is kept: a cell is at least r_cut + dr_max_tolerable wide
-// (stoermer:75), the same skin argument that keeps the reference's lists valid.
+// way.  Whenever the reference would rebuild its lists (the displacement
+// trigger of module_stoermer_verlet_method.f08:177-185 fired), all particles
+// are re-binned on the reference's own grid (nint(area/cell) cells, index
+// ceiling(x/cell), pm:62, 95): perm lists the particles cell by cell (x
+// fastest), so the 27-cell neighbourhood of a particle is nine contiguous runs
+// of slots.  Between rebuilds the binning is kept: a cell is at least
+// r_cut + dr_max_tolerable wide (stoermer:75), the same skin argument that
+// keeps the reference's lists valid.  Every step a cell-ordered copy of the
+// current positions (posj) is gathered through perm.
 //
-// The force kernel gives one lane one particle and one warp 32 consecutive
-// slots; see cell_force_kernel below.
+// Ownership is by PARTICLE INDEX (the i-sharding of the all-pairs path), so a
+// sharded run needs no communication beyond the per-step position all-gather:
+// every rank bins all particles redundantly (same data, deterministic order,
+// same result) and walks its own particles in cell order through own_slots.
 //
-// Everything here is conditional ON THE DEVICE: the re-binning kernels read
-// the rebuild flag from the control block and return at once when it is clear,
-// so the host never has to synchronise to learn whether a rebuild happened.
+// Everything is conditional ON THE DEVICE: the housekeeping kernel evaluates
+// the trigger itself and only then runs its grid-synchronised re-binning
+// phases, so the host never synchronises to learn whether a rebuild happened,
+// and a step is two launches: force (+kick+drift) and housekeeping.
 #pragma once
+
+#include <cooperative_groups.h>
 
 #include "psim_allpairs.cuh"
 #include "psim_allpairs2.cuh"
@@ -28,127 +36,6 @@ template <class R>
 __device__ __forceinline__ int clamp_cell(R x, R cell, int nc) {
   int c = (int)r_ceil(r_div(x, cell));
   return c < 1 ? 1 : (c > nc ? nc : c);
-}
-
-// K1: binned cell of every slot (inactive -> tail bucket ncell) + histogram.
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-cells_key_kernel(const Real4<R>* __restrict__ pos, int32_t* __restrict__ key, unsigned* __restrict__ count,
-                 int64_t n, int ncell, Consts<R> c, const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int64_t k = (int64_t)blockIdx.x * T + threadIdx.x;
-  if (k >= n) return;
-  const Real4<R> p = pos[k];
-  int cell = ncell;
-  if (!(p.w >= c.huge)) {
-    const int cx = clamp_cell(p.x, c.cell[0], c.nc[0]);
-    const int cy = clamp_cell(p.y, c.cell[1], c.nc[1]);
-    const int cz = clamp_cell(p.z, c.cell[2], c.nc[2]);
-    cell = (cx - 1) + c.nc[0] * ((cy - 1) + c.nc[1] * (cz - 1));
-  }
-  key[k] = cell;
-  atomicAdd(&count[cell], 1u);
-}
-
-// K2: exclusive scan of the histogram (one block; ncell+1 buckets).
-__global__ void __launch_bounds__(1024)
-cells_scan_kernel(const unsigned* __restrict__ count, int32_t* __restrict__ cell_start, unsigned* __restrict__ fill,
-                  int nbuckets, const int* flag, int force) {
-  if (!force && !*flag) return;
-  __shared__ unsigned s_sum[1024];
-  const int tid = threadIdx.x;
-  const int per = (nbuckets + 1023) / 1024;
-  const int lo = tid * per, hi = min(nbuckets, lo + per);
-  unsigned sum = 0;
-  for (int b = lo; b < hi; ++b) sum += count[b];
-  s_sum[tid] = sum;
-  __syncthreads();
-  for (int off = 1; off < 1024; off <<= 1) {      // Hillis-Steele inclusive scan
-    unsigned v = tid >= off ? s_sum[tid - off] : 0u;
-    __syncthreads();
-    s_sum[tid] += v;
-    __syncthreads();
-  }
-  unsigned run = s_sum[tid] - sum;                // exclusive prefix of this thread's chunk
-  for (int b = lo; b < hi; ++b) {
-    cell_start[b] = (int32_t)run;
-    run += count[b];
-    fill[b] = 0u;
-  }
-  if (tid == 1023) cell_start[nbuckets] = (int32_t)s_sum[1023];
-}
-
-// K3: scatter slots into their cell segment (order inside a cell fixed by K4).
-template <int T>
-__global__ void __launch_bounds__(T)
-cells_scatter_kernel(const int32_t* __restrict__ key, const int32_t* __restrict__ cell_start,
-                     unsigned* __restrict__ fill, int32_t* __restrict__ src, int64_t n, const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int64_t k = (int64_t)blockIdx.x * T + threadIdx.x;
-  if (k >= n) return;
-  const int cell = key[k];
-  const unsigned at = atomicAdd(&fill[cell], 1u);
-  src[cell_start[cell] + at] = (int32_t)k;
-}
-
-// K4: make the order inside every cell deterministic (ascending previous slot)
-// and clear the histogram for the next rebuild.  One thread per bucket; the
-// tail bucket of inactive particles is left unsorted (it never contributes).
-template <int T>
-__global__ void __launch_bounds__(T)
-cells_order_kernel(const int32_t* __restrict__ cell_start, int32_t* __restrict__ src, unsigned* __restrict__ count,
-                   int ncell, const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int cell = blockIdx.x * T + threadIdx.x;
-  if (cell > ncell) return;
-  count[cell] = 0u;
-  if (cell == ncell) return;
-  const int lo = cell_start[cell], hi = cell_start[cell + 1];
-  for (int a = lo + 1; a < hi; ++a) {
-    const int32_t v = src[a];
-    int b = a - 1;
-    while (b >= lo && src[b] > v) { src[b + 1] = src[b]; --b; }
-    src[b + 1] = v;
-  }
-}
-
-template <class R>
-struct CellArrays {
-  Real4<R>* a[5];     // pos, vel, f_old, f_new, disp
-  int32_t* orig;
-  int32_t* cell_of;
-};
-
-// K5: gather the state into the spare set in the new order; K6: copy it back.
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-cells_gather_kernel(CellArrays<R> from, CellArrays<R> to, const int32_t* __restrict__ src,
-                    const int32_t* __restrict__ key, int64_t n, const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int64_t k = (int64_t)blockIdx.x * T + threadIdx.x;
-  if (k >= n) return;
-  const int32_t s = src[k];
-#pragma unroll
-  for (int q = 0; q < 5; ++q) to.a[q][k] = from.a[q][s];
-  to.orig[k] = from.orig[s];
-  to.cell_of[k] = key[s];
-}
-
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-cells_copyback_kernel(CellArrays<R> from, CellArrays<R> to, int64_t n, const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int64_t k = (int64_t)blockIdx.x * T + threadIdx.x;
-  if (k >= n) return;
-#pragma unroll
-  for (int q = 0; q < 5; ++q) to.a[q][k] = from.a[q][k];
-  to.orig[k] = from.orig[k];
-  to.cell_of[k] = from.cell_of[k];
-}
-
-__global__ void iota_kernel(int32_t* p, int64_t n) {
-  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < n) p[k] = (int32_t)k;
 }
 
 // The force pass over the binned state.
@@ -168,17 +55,16 @@ __global__ void iota_kernel(int32_t* p, int64_t n) {
 // Phase 2 walks the queue with the exact pair term in the working precision.
 // Sums run in ascending slot order: deterministic.
 //
-// INDEXED = false: the state itself is in cell order (single GPU): slot k holds
-// particle k of the permuted arrays and posj is a.pos_cur.
-// INDEXED = true (sharded runs): the state stays in particle order; posj is a
-// cell-ordered COPY of all positions, perm maps slot -> particle, and the block
-// walks own_slots, the cell-ordered list of the slots whose particle this rank
-// owns.  The force sum uses slots, the kick/drift epilogue the particle index.
-template <class R, int MODE, int QCAP, int T, bool INDEXED>
+// The particle state stays in particle (array) order.  posj is a cell-ordered
+// COPY of all positions, perm maps slot -> particle, and the block walks
+// own_slots, the cell-ordered list of the slots whose particle this rank owns
+// (all of them on a single GPU).  The force sum works on slots, the kick/drift
+// epilogue on the particle index.
+template <class R, int MODE, int QCAP, int T>
 __global__ void __launch_bounds__(T)
 cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const int32_t* __restrict__ cell_of,
                   const int32_t* __restrict__ cell_start, const int32_t* __restrict__ own_slots,
-                  const int32_t* __restrict__ own_start, const int32_t* __restrict__ perm, int ncell, int64_t n) {
+                  const int32_t* __restrict__ own_start, const int32_t* __restrict__ perm, int ncell) {
   constexpr int W = T / 32, TJ = 32;
   __shared__ int32_t queue[QCAP * T];
   __shared__ __align__(16) float tx[W][2][TJ], ty[W][2][TJ], tz[W][2][TJ], tw[W][2][TJ];
@@ -187,11 +73,7 @@ cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const 
   const int64_t idx = (int64_t)blockIdx.x * T + tid;
   int64_t k = -1;              // slot in cell order (j-side numbering)
   int64_t ip = -1;             // particle index in the state arrays (epilogue numbering)
-  if (INDEXED) {
-    if (idx < own_start[ncell]) { k = own_slots[idx]; ip = perm[k]; }
-  } else if (idx < n) {
-    k = idx; ip = idx;
-  }
+  if (idx < own_start[ncell]) { k = own_slots[idx]; ip = perm[k]; }
   const float rcut = (float)c.r_cut;
   const float cut2f = (float)c.cut2_pad * (1.0f + 1.0e-6f);
 
@@ -308,121 +190,191 @@ cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const 
 
   R first = (R)0, second = (R)0;
   if (ip >= 0) step_epilogue<R, MODE>(a, ip, fx, fy, fz, first, second);
-  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part);
+  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, T>(first, second, a.top2_part, a.ticket, a.rank_pair);
 }
 
-// ---- sharded runs: binning by index, state stays in particle order ------------
 
-// S1: cell of every PARTICLE (inactive -> tail bucket) + histograms of all and of owned particles.
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-cellsx_key_kernel(const Real4<R>* __restrict__ pos, int32_t* __restrict__ key, unsigned* __restrict__ count,
-                  unsigned* __restrict__ own_count, int64_t n, int64_t i_lo, int64_t i_hi, int ncell, Consts<R> c,
-                  const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
-  if (i >= n) return;
-  const Real4<R> p = pos[i];
-  int cell = ncell;
-  if (!(p.w >= c.huge)) {
-    const int cx = clamp_cell(p.x, c.cell[0], c.nc[0]);
-    const int cy = clamp_cell(p.y, c.cell[1], c.nc[1]);
-    const int cz = clamp_cell(p.z, c.cell[2], c.nc[2]);
-    cell = (cx - 1) + c.nc[0] * ((cy - 1) + c.nc[1] * (cz - 1));
+// ---- housekeeping: trigger, rebuild side effects, re-binning, position copy --------
+
+template <class R>
+struct HouseArgs {
+  Real4<R>* pos_new;      // the buffer the drift just filled (the current one from here on)
+  Real4<R>* pos_other;    // the other buffer: next step's target
+  Real4<R>* disp;
+  const R* rank_pairs;    // [2 * world] every rank's two largest |disp| (null: no trigger this call)
+  int world;
+  int flag_in_ctrl;       // NB_OF_THREADS > 1: slice_trigger_kernel already wrote ctrl->flag[parity]
+  Control* ctrl;
+  int parity;
+  int64_t n, i_lo, i_hi;
+  Consts<R> c;
+  // cell path (cells == 0: all-pairs, nothing to bin)
+  int cells, force_rebin, ncell;
+  int32_t *key, *perm, *cell_start, *own_start, *cell_of, *own_slots;
+  unsigned *count, *own_count, *fill;
+  Real4<R>* posj;
+};
+
+// exclusive scan of cnt[0..nb) into start[0..nb] by ONE block of 256 threads
+__device__ __forceinline__ void block_scan_256(const unsigned* cnt, int32_t* start, unsigned* zero_me, int nb,
+                                               unsigned* s_sum) {
+  const int tid = threadIdx.x;
+  const int per = (nb + 255) / 256;
+  const int lo = tid * per, hi = min(nb, lo + per);
+  unsigned sum = 0;
+  for (int b = lo; b < hi; ++b) sum += cnt[b];
+  s_sum[tid] = sum;
+  __syncthreads();
+  for (int off = 1; off < 256; off <<= 1) {
+    const unsigned v = tid >= off ? s_sum[tid - off] : 0u;
+    __syncthreads();
+    s_sum[tid] += v;
+    __syncthreads();
   }
-  key[i] = cell;
-  atomicAdd(&count[cell], 1u);
-  if (i >= i_lo && i < i_hi && cell < ncell) atomicAdd(&own_count[cell], 1u);
+  unsigned run = s_sum[tid] - sum;
+  for (int b = lo; b < hi; ++b) {
+    start[b] = (int32_t)run;
+    run += cnt[b];
+    if (zero_me) zero_me[b] = 0u;
+  }
+  if (tid == 255) start[nb] = (int32_t)s_sum[255];
+  __syncthreads();
 }
 
-// S4: per cell, put the slot -> particle map in ascending particle order (deterministic),
-// record the cell of every slot, and list the slots of the owned particles in cell order.
-template <int T>
-__global__ void __launch_bounds__(T)
-cellsx_order_kernel(const int32_t* __restrict__ cell_start, const int32_t* __restrict__ own_start,
-                    int32_t* __restrict__ perm, int32_t* __restrict__ cell_of, int32_t* __restrict__ own_slots,
-                    unsigned* __restrict__ count, unsigned* __restrict__ own_count, int64_t i_lo, int64_t i_hi,
-                    int ncell, const int* flag, int force) {
-  if (!force && !*flag) return;
-  const int cell = blockIdx.x * T + threadIdx.x;
-  if (cell > ncell) return;
-  count[cell] = 0u;
-  own_count[cell] = 0u;
-  const int lo = cell_start[cell], hi = cell_start[cell + 1];
-  if (cell == ncell) {                     // inactive tail: never read through the cell tables
-    for (int a = lo; a < hi; ++a) cell_of[a] = ncell;
-    return;
-  }
-  for (int a = lo + 1; a < hi; ++a) {
-    const int32_t v = perm[a];
-    int b = a - 1;
-    while (b >= lo && perm[b] > v) { perm[b + 1] = perm[b]; --b; }
-    perm[b + 1] = v;
-  }
-  int m = own_start[cell];
-  for (int a = lo; a < hi; ++a) {
-    cell_of[a] = cell;
-    const int32_t i = perm[a];
-    if (i >= i_lo && i < i_hi) own_slots[m++] = a;
-  }
-}
+// One cooperative launch per step (256 threads per block, grid = what is co-resident).
+//  1. trigger: dr_max_first + dr_max_second > dr_max_tolerable over the merged per-rank pairs
+//     (stoermer:168-185); every block computes it for itself from <= 8 pairs.
+//  2. if it fired: the observable side effects of update_neighbor_list_and_cell_space
+//     (pm:112-124): displacement reset (pm:158), deactivation of particles whose cell index left
+//     the grid (pm:440-441, 503-504, 534-552);
+//  3. cell path, if it fired (or on demand): histogram -> scan -> scatter -> per-cell order,
+//     separated by grid-wide barriers;
+//  4. cell path, always: posj = positions in cell order; owned inactive records are carried
+//     into the other position buffer (they are not in own_slots, so no force block does it).
+template <class R>
+__global__ void __launch_bounds__(256)
+housekeeping_kernel(const HouseArgs<R> h) {
+  namespace cgn = cooperative_groups;
+  cgn::grid_group grid = cgn::this_grid();
+  __shared__ unsigned s_sum[256];
+  const Consts<R>& c = h.c;
+  const int64_t gtid = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  const int64_t gsz = (int64_t)gridDim.x * 256;
 
-// every step: the cell-ordered copy of all positions
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-cellsx_gather_kernel(Real4<R>* __restrict__ posj, const Real4<R>* __restrict__ pos,
-                     const int32_t* __restrict__ perm, int64_t n) {
-  const int64_t k = (int64_t)blockIdx.x * T + threadIdx.x;
-  if (k < n) posj[k] = pos[perm[k]];
-}
+  int flag = 0;
+  if (h.flag_in_ctrl) {
+    flag = h.ctrl->flag[h.parity];
+  } else if (h.rank_pairs) {
+    R first = (R)0, second = (R)0;
+    for (int r = 0; r < 2 * h.world; ++r) top2_push(first, second, h.rank_pairs[r]);
+    flag = r_add(first, second) > c.dr_max_tolerable ? 1 : 0;
+  }
+  if (gtid == 0) {
+    if (!h.flag_in_ctrl) h.ctrl->flag[h.parity] = flag;
+    if (flag) h.ctrl->rebuilds += 1;
+  }
+  if (gtid == 1 || (gtid == 0 && gsz == 1)) h.ctrl->flag[h.parity ^ 1] = 0;
+  const bool rebin = h.cells && (flag || h.force_rebin);
 
-// every fused step of a sharded run: owned INACTIVE particles are not in own_slots, so their
-// (frozen) record is carried into the next position buffer here
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-cellsx_carry_inactive_kernel(const Real4<R>* __restrict__ pos_cur, Real4<R>* __restrict__ pos_nxt,
-                             int64_t i_lo, int64_t i_hi, Consts<R> c) {
-  const int64_t i = i_lo + (int64_t)blockIdx.x * T + threadIdx.x;
-  if (i >= i_hi) return;
-  const Real4<R> p = pos_cur[i];
-  if (p.w >= c.huge) pos_nxt[i] = p;
+  if (flag || rebin) {
+    for (int64_t i = gtid; i < h.n; i += gsz) {
+      Real4<R> p = h.pos_new[i];
+      bool active = !(p.w >= c.huge);
+      if (flag && active) {
+        if (inside_grid(p.x, p.y, p.z, c)) {
+          if (i >= h.i_lo && i < h.i_hi) { Real4<R> z; z.x = z.y = z.z = z.w = (R)0; h.disp[i] = z; }
+        } else {
+          p.w = c.huge;
+          h.pos_new[i] = p;
+          active = false;
+        }
+      }
+      if (rebin) {
+        int cell = h.ncell;
+        if (active) {
+          const int cx = clamp_cell(p.x, c.cell[0], c.nc[0]);
+          const int cy = clamp_cell(p.y, c.cell[1], c.nc[1]);
+          const int cz = clamp_cell(p.z, c.cell[2], c.nc[2]);
+          cell = (cx - 1) + c.nc[0] * ((cy - 1) + c.nc[1] * (cz - 1));
+        }
+        h.key[i] = cell;
+        atomicAdd(&h.count[cell], 1u);
+        if (i >= h.i_lo && i < h.i_hi && cell < h.ncell) atomicAdd(&h.own_count[cell], 1u);
+      }
+    }
+  }
+
+  if (rebin) {
+    grid.sync();
+    if (blockIdx.x == 0) {
+      block_scan_256(h.count, h.cell_start, h.fill, h.ncell + 1, s_sum);
+      block_scan_256(h.own_count, h.own_start, nullptr, h.ncell + 1, s_sum);
+    }
+    grid.sync();
+    for (int64_t i = gtid; i < h.n; i += gsz) {
+      const int cell = h.key[i];
+      h.perm[h.cell_start[cell] + atomicAdd(&h.fill[cell], 1u)] = (int32_t)i;
+    }
+    grid.sync();
+    // per cell: ascending particle order (deterministic), cell of every slot, owned slots in cell order
+    for (int64_t cell = gtid; cell <= h.ncell; cell += gsz) {
+      h.count[cell] = 0u;
+      h.own_count[cell] = 0u;
+      const int lo = h.cell_start[cell], hi = h.cell_start[cell + 1];
+      if (cell == h.ncell) {                       // inactive tail: never read through the cell tables
+        for (int a = lo; a < hi; ++a) h.cell_of[a] = h.ncell;
+        continue;
+      }
+      for (int a = lo + 1; a < hi; ++a) {
+        const int32_t v = h.perm[a];
+        int b = a - 1;
+        while (b >= lo && h.perm[b] > v) { h.perm[b + 1] = h.perm[b]; --b; }
+        h.perm[b + 1] = v;
+      }
+      int m = h.own_start[cell];
+      for (int a = lo; a < hi; ++a) {
+        h.cell_of[a] = (int32_t)cell;
+        const int32_t i = h.perm[a];
+        if (i >= h.i_lo && i < h.i_hi) h.own_slots[m++] = a;
+      }
+    }
+    grid.sync();
+  }
+
+  if (h.cells) {
+    for (int64_t k = gtid; k < h.n; k += gsz) h.posj[k] = h.pos_new[h.perm[k]];
+    for (int64_t i = h.i_lo + gtid; i < h.i_hi; i += gsz) {
+      const Real4<R> p = h.pos_new[i];
+      if (p.w >= c.huge) h.pos_other[i] = p;
+    }
+  }
 }
 
 template <class R>
 struct CellPath {
-  static constexpr int T = 128;          // threads of the re-binning kernels
   static constexpr int TF = 64;          // threads of the force kernel (two autonomous warps)
   static constexpr int QCAP = 96;        // queue entries per lane
   int64_t launches = 0;
   int64_t n = 0, n_pad = 0;
   int ncell = 0;
-  bool binned = false;
-  int32_t *key = nullptr, *src = nullptr, *cell_start = nullptr;
-  unsigned *count = nullptr, *fill = nullptr;
-  int32_t *orig = nullptr, *cell_of = nullptr;
-  CellArrays<R> spare = {};
-  // indexed (sharded) mode: state stays in particle order
-  bool indexed = false;
+  bool binned = false;                   // perm / posj are valid for the current positions
+  int32_t *key = nullptr, *perm = nullptr, *cell_start = nullptr, *own_start = nullptr;
+  int32_t *cell_of = nullptr, *own_slots = nullptr;
+  unsigned *count = nullptr, *own_count = nullptr, *fill = nullptr;
   Real4<R>* posj = nullptr;
-  int32_t *own_slots = nullptr, *own_start = nullptr;
-  unsigned* own_count = nullptr;
 
   bool allocated() const { return key != nullptr; }
-  const int32_t* orig_or_null() const { return indexed ? nullptr : orig; }
+  const int32_t* orig_or_null() const { return nullptr; }   // the state is always in array order
 
   void destroy() {
-    cudaFree(key); cudaFree(src); cudaFree(cell_start); cudaFree(count); cudaFree(fill);
-    cudaFree(orig); cudaFree(cell_of);
-    for (int q = 0; q < 5; ++q) cudaFree(spare.a[q]);
-    cudaFree(spare.orig); cudaFree(spare.cell_of);
-    cudaFree(posj); cudaFree(own_slots); cudaFree(own_start); cudaFree(own_count);
-    key = src = cell_start = nullptr; count = fill = nullptr; orig = cell_of = nullptr;
-    posj = nullptr; own_slots = own_start = nullptr; own_count = nullptr;
-    spare = CellArrays<R>();
+    cudaFree(key); cudaFree(perm); cudaFree(cell_start); cudaFree(own_start); cudaFree(cell_of);
+    cudaFree(own_slots); cudaFree(count); cudaFree(own_count); cudaFree(fill); cudaFree(posj);
+    key = perm = cell_start = own_start = cell_of = own_slots = nullptr;
+    count = own_count = fill = nullptr; posj = nullptr;
     binned = false;
   }
 
-  // positions were replaced wholesale: the next force pass must re-bin
+  // positions were replaced wholesale (or the algorithm was switched): re-bin before the next force pass
   void invalidate() { binned = false; }
 
   template <class S>
@@ -430,116 +382,52 @@ struct CellPath {
     if (allocated()) return cudaSuccess;
     n = sim.n; n_pad = sim.n_pad;
     ncell = sim.c.nc[0] * sim.c.nc[1] * sim.c.nc[2];
-    indexed = sim.world > 1 || sim.cells_indexed;
     cudaError_t e;
 #define PSIM_TRY(x) if ((e = (x)) != cudaSuccess) return e
-    if (indexed) {
-      PSIM_TRY(cudaMalloc(&key, sizeof(int32_t) * n_pad));
-      PSIM_TRY(cudaMalloc(&src, sizeof(int32_t) * n_pad));            // perm: slot -> particle
-      PSIM_TRY(cudaMalloc(&cell_start, sizeof(int32_t) * (ncell + 2)));
-      PSIM_TRY(cudaMalloc(&own_start, sizeof(int32_t) * (ncell + 2)));
-      PSIM_TRY(cudaMalloc(&count, sizeof(unsigned) * (ncell + 1)));
-      PSIM_TRY(cudaMalloc(&own_count, sizeof(unsigned) * (ncell + 1)));
-      PSIM_TRY(cudaMalloc(&fill, sizeof(unsigned) * (ncell + 1)));
-      PSIM_TRY(cudaMalloc(&cell_of, sizeof(int32_t) * n_pad));
-      PSIM_TRY(cudaMalloc(&own_slots, sizeof(int32_t) * n_pad));
-      PSIM_TRY(cudaMalloc(&posj, sizeof(Real4<R>) * n_pad));
-      PSIM_TRY(cudaMemsetAsync(count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
-      PSIM_TRY(cudaMemsetAsync(own_count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
-      binned = false;
-      return cudaSuccess;
-    }
     PSIM_TRY(cudaMalloc(&key, sizeof(int32_t) * n_pad));
-    PSIM_TRY(cudaMalloc(&src, sizeof(int32_t) * n_pad));
+    PSIM_TRY(cudaMalloc(&perm, sizeof(int32_t) * n_pad));
     PSIM_TRY(cudaMalloc(&cell_start, sizeof(int32_t) * (ncell + 2)));
+    PSIM_TRY(cudaMalloc(&own_start, sizeof(int32_t) * (ncell + 2)));
     PSIM_TRY(cudaMalloc(&count, sizeof(unsigned) * (ncell + 1)));
+    PSIM_TRY(cudaMalloc(&own_count, sizeof(unsigned) * (ncell + 1)));
     PSIM_TRY(cudaMalloc(&fill, sizeof(unsigned) * (ncell + 1)));
-    PSIM_TRY(cudaMalloc(&orig, sizeof(int32_t) * n_pad));
     PSIM_TRY(cudaMalloc(&cell_of, sizeof(int32_t) * n_pad));
-    for (int q = 0; q < 5; ++q) PSIM_TRY(cudaMalloc(&spare.a[q], sizeof(Real4<R>) * n_pad));
-    PSIM_TRY(cudaMalloc(&spare.orig, sizeof(int32_t) * n_pad));
-    PSIM_TRY(cudaMalloc(&spare.cell_of, sizeof(int32_t) * n_pad));
+    PSIM_TRY(cudaMalloc(&own_slots, sizeof(int32_t) * n_pad));
+    PSIM_TRY(cudaMalloc(&posj, sizeof(Real4<R>) * n_pad));
     PSIM_TRY(cudaMemsetAsync(count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
-    PSIM_TRY(cudaMemsetAsync(cell_of, 0, sizeof(int32_t) * n_pad, sim.stream));
+    PSIM_TRY(cudaMemsetAsync(own_count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
+    PSIM_TRY(cudaMemsetAsync(own_start, 0, sizeof(int32_t) * (ncell + 2), sim.stream));
 #undef PSIM_TRY
-    iota_kernel<<<(unsigned)((n_pad + 255) / 256), 256, 0, sim.stream>>>(orig, n_pad);
-    ++launches;
     binned = false;
     return cudaSuccess;
   }
 
-  // Re-order the state held in (posbuf, vel, f_old, f_new, disp) by cell, if
-  // the rebuild flag of this step is set (or unconditionally with force).
-  template <class S>
-  void rebin(S& sim, Real4<R>* posbuf, int parity, bool force) {
-    const int* flag = &sim.ctrl->flag[parity];
-    const int f = force ? 1 : 0;
-    const unsigned gn = (unsigned)((n + T - 1) / T);
-    cudaStream_t st = sim.stream;
-    if (indexed) {
-      cellsx_key_kernel<R, T><<<gn, T, 0, st>>>(posbuf, key, count, own_count, n, sim.i_lo, sim.i_hi, ncell, sim.c, flag, f);
-      cells_scan_kernel<<<1, 1024, 0, st>>>(count, cell_start, fill, ncell + 1, flag, f);
-      cells_scan_kernel<<<1, 1024, 0, st>>>(own_count, own_start, fill, ncell + 1, flag, f);
-      cells_scatter_kernel<T><<<gn, T, 0, st>>>(key, cell_start, fill, src, n, flag, f);
-      cellsx_order_kernel<T><<<(unsigned)((ncell + 1 + T - 1) / T), T, 0, st>>>(
-          cell_start, own_start, src, cell_of, own_slots, count, own_count, sim.i_lo, sim.i_hi, ncell, flag, f);
-      launches += 5;
-      if (force) binned = true;
-      return;
-    }
-    cells_key_kernel<R, T><<<gn, T, 0, st>>>(posbuf, key, count, n, ncell, sim.c, flag, f);
-    cells_scan_kernel<<<1, 1024, 0, st>>>(count, cell_start, fill, ncell + 1, flag, f);
-    cells_scatter_kernel<T><<<gn, T, 0, st>>>(key, cell_start, fill, src, n, flag, f);
-    cells_order_kernel<T><<<(unsigned)((ncell + 1 + T - 1) / T), T, 0, st>>>(cell_start, src, count, ncell, flag, f);
-    CellArrays<R> live;
-    live.a[0] = posbuf; live.a[1] = sim.vel; live.a[2] = sim.f_old; live.a[3] = sim.f_new; live.a[4] = sim.disp;
-    live.orig = orig; live.cell_of = cell_of;
-    cells_gather_kernel<R, T><<<gn, T, 0, st>>>(live, spare, src, key, n, flag, f);
-    cells_copyback_kernel<R, T><<<gn, T, 0, st>>>(spare, live, n, flag, f);
-    launches += 6;
-    if (force) binned = true;
+  void fill_args(HouseArgs<R>& h) const {
+    h.ncell = ncell;
+    h.key = key; h.perm = perm; h.cell_start = cell_start; h.own_start = own_start; h.cell_of = cell_of;
+    h.own_slots = own_slots; h.count = count; h.own_count = own_count; h.fill = fill; h.posj = posj;
   }
 
   template <class S>
   psim_status force(S& sim, int mode) {
     if (ensure(sim) != cudaSuccess) return PSIM_ERR_CUDA;
-    if (!binned) rebin(sim, sim.pos[sim.cur], 0, true);
+    if (!binned) {                         // first use, new positions, or the algorithm was just selected
+      psim_status st = sim.launch_housekeeping(sim.pos[sim.cur], sim.pos[sim.cur ^ 1], false, true);
+      if (st != PSIM_OK) return st;
+    }
     const StepArgs<R> a = sim.step_args();
-    if (indexed) {
-      const int64_t n_own = sim.i_hi - sim.i_lo;
-      if (n_own <= 0) { if (mode == MODE_FORCE_KICK_DRIFT) sim.top2_count = 0; return PSIM_OK; }
-      const unsigned gn = (unsigned)((n + T - 1) / T);
-      cellsx_gather_kernel<R, T><<<gn, T, 0, sim.stream>>>(posj, a.pos_cur, src, n);
-      const unsigned grid = (unsigned)((n_own + TF - 1) / TF);
-      if (mode == MODE_FORCE)
-        cell_force_kernel<R, MODE_FORCE, QCAP, TF, true><<<grid, TF, 0, sim.stream>>>(
-            a, posj, cell_of, cell_start, own_slots, own_start, src, ncell, n);
-      else if (mode == MODE_FORCE_KICK)
-        cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF, true><<<grid, TF, 0, sim.stream>>>(
-            a, posj, cell_of, cell_start, own_slots, own_start, src, ncell, n);
-      else {
-        cellsx_carry_inactive_kernel<R, T><<<(unsigned)((n_own + T - 1) / T), T, 0, sim.stream>>>(
-            a.pos_cur, a.pos_nxt, sim.i_lo, sim.i_hi, sim.c);
-        cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF, true><<<grid, TF, 0, sim.stream>>>(
-            a, posj, cell_of, cell_start, own_slots, own_start, src, ncell, n);
-        sim.top2_count = grid;
-        ++launches;
-      }
-      launches += 2;
-      return PSIM_OK;
-    }
-    const unsigned grid = (unsigned)((n + TF - 1) / TF);
+    const int64_t n_own = sim.i_hi - sim.i_lo;
+    if (n_own <= 0) return PSIM_OK;
+    const unsigned grid = (unsigned)((n_own + TF - 1) / TF);
     if (mode == MODE_FORCE)
-      cell_force_kernel<R, MODE_FORCE, QCAP, TF, false><<<grid, TF, 0, sim.stream>>>(
-          a, a.pos_cur, cell_of, cell_start, nullptr, nullptr, nullptr, ncell, n);
+      cell_force_kernel<R, MODE_FORCE, QCAP, TF><<<grid, TF, 0, sim.stream>>>(
+          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell);
     else if (mode == MODE_FORCE_KICK)
-      cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF, false><<<grid, TF, 0, sim.stream>>>(
-          a, a.pos_cur, cell_of, cell_start, nullptr, nullptr, nullptr, ncell, n);
-    else {
-      cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF, false><<<grid, TF, 0, sim.stream>>>(
-          a, a.pos_cur, cell_of, cell_start, nullptr, nullptr, nullptr, ncell, n);
-      sim.top2_count = grid;
-    }
+      cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF><<<grid, TF, 0, sim.stream>>>(
+          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell);
+    else
+      cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF><<<grid, TF, 0, sim.stream>>>(
+          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell);
     ++launches;
     return PSIM_OK;
   }

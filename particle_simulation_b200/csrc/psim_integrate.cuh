@@ -13,6 +13,8 @@ struct Control {
   int flag[2];                  // rebuild flag of the current / next step (indexed by step parity)
   unsigned long long rebuilds;  // times the trigger fired
   unsigned long long n_active;  // scratch for counting
+  unsigned ticket;              // last-block hand-over of the top-2 reduction
+  unsigned pad;
 };
 
 // compute_locations (module_stoermer_verlet_method.f08:136-187) for the owned slice.
@@ -20,7 +22,8 @@ template <class R, int T>
 __global__ void __launch_bounds__(T)
 drift_kernel(const Real4<R>* __restrict__ pos_cur, Real4<R>* __restrict__ pos_nxt,
              const Real4<R>* __restrict__ vel, Real4<R>* __restrict__ f_old, Real4<R>* __restrict__ f_new,
-             Real4<R>* __restrict__ disp, R* __restrict__ top2_part, int64_t i_lo, int64_t i_hi, Consts<R> c) {
+             Real4<R>* __restrict__ disp, R* __restrict__ top2_part, unsigned* ticket, R* rank_pair,
+             int64_t i_lo, int64_t i_hi, Consts<R> c) {
   const int64_t i = i_lo + (int64_t)blockIdx.x * T + threadIdx.x;
   R first = (R)0, second = (R)0;
   if (i < i_hi) {
@@ -39,7 +42,7 @@ drift_kernel(const Real4<R>* __restrict__ pos_cur, Real4<R>* __restrict__ pos_nx
       first = dr;
     }
   }
-  block_top2_store<R, T>(first, second, top2_part);
+  block_top2_store<R, T>(first, second, top2_part, ticket, rank_pair);
 }
 
 // compute_velocities (module_stoermer_verlet_method.f08:191-206).
@@ -58,41 +61,10 @@ kick_kernel(const Real4<R>* __restrict__ pos, Real4<R>* __restrict__ vel, const 
   vel[i] = v;
 }
 
-// Merge `count` (first, second) pairs into one.  One block.
-//   out_pair != nullptr : write the merged pair there (a rank's contribution
-//                         to the cross-GPU exchange)
-//   out_pair == nullptr : this is the final merge — evaluate
-//                         dr_max_first + dr_max_second > dr_max_tolerable
-//                         (stoermer:177-185) into ctrl->flag[parity]
-template <class R>
-__global__ void __launch_bounds__(256)
-top2_merge_kernel(const R* __restrict__ pairs, int64_t count, R* out_pair, Control* ctrl, int parity,
-                  Consts<R> c) {
-  __shared__ R s_first[8], s_second[8];
-  R first = (R)0, second = (R)0;
-  for (int64_t k = threadIdx.x; k < count; k += 256) {
-    top2_push(first, second, pairs[2 * k]);
-    top2_push(first, second, pairs[2 * k + 1]);
-  }
-  top2_warp_reduce(first, second);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) { s_first[warp] = first; s_second[warp] = second; }
-  __syncthreads();
-  if (warp == 0) {
-    first = lane < 8 ? s_first[lane] : (R)0;
-    second = lane < 8 ? s_second[lane] : (R)0;
-    top2_warp_reduce(first, second);
-    if (lane == 0) {
-      if (out_pair) { out_pair[0] = first; out_pair[1] = second; }
-      else ctrl->flag[parity] = (r_add(first, second) > c.dr_max_tolerable) ? 1 : 0;
-    }
-  }
-}
-
 // NB_OF_THREADS > 1: the reference evaluates the trigger per thread slice
 // (program_particle_simulation_openmp.f08:71,86,92; slices :305-323).  One
 // block per slice scans |disp| (disp.w) of its slice and ORs its verdict in.
-// ctrl->flag[parity] must be 0 on entry (the effects kernel of the previous
+// ctrl->flag[parity] must be 0 on entry (the housekeeping kernel of the previous
 // step clears it).
 template <class R>
 __global__ void __launch_bounds__(256)
@@ -122,32 +94,6 @@ slice_trigger_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restric
     second = lane < 8 ? s_second[lane] : (R)0;
     top2_warp_reduce(first, second);
     if (lane == 0 && r_add(first, second) > c.dr_max_tolerable) atomicOr(&ctrl->flag[parity], 1);
-  }
-}
-
-// What update_neighbor_list_and_cell_space (module_particle_management.f08:112-124)
-// leaves visible to the integrator when the trigger fired: displacement reset
-// for particles still in the grid (:158) and deactivation of those whose cell
-// index left 1..nc (:440-441, 503-504, 534-552).  Runs over ALL particles' x
-// (every rank holds all positions); disp is touched for the owned slice only.
-template <class R, int T>
-__global__ void __launch_bounds__(T)
-rebuild_effects_kernel(Real4<R>* __restrict__ pos, Real4<R>* __restrict__ disp, int64_t n,
-                       int64_t i_lo, int64_t i_hi, Control* ctrl, int parity, Consts<R> c) {
-  const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
-  const int flag = ctrl->flag[parity];
-  if (i == 0) {
-    ctrl->flag[parity ^ 1] = 0;
-    if (flag) ctrl->rebuilds += 1;
-  }
-  if (!flag || i >= n) return;
-  Real4<R> p = pos[i];
-  if (p.w >= c.huge) return;
-  if (inside_grid(p.x, p.y, p.z, c)) {
-    if (i >= i_lo && i < i_hi) { Real4<R> z; z.x = z.y = z.z = z.w = (R)0; disp[i] = z; }
-  } else {
-    p.w = c.huge;
-    pos[i] = p;
   }
 }
 

@@ -21,7 +21,7 @@ from . import build as _build
 
 STATUS_OK = 0
 FORCE_ALL_PAIRS, FORCE_CELL_BINNED = 0, 1
-OPT_FORCE_ALGO, OPT_FUSED_STEP, OPT_KERNEL_TIMING, OPT_EXACT_DIFF_FILTER, OPT_CELLS_INDEXED = 0, 1, 2, 3, 4
+OPT_FORCE_ALGO, OPT_FUSED_STEP, OPT_KERNEL_TIMING, OPT_EXACT_DIFF_FILTER = 0, 1, 2, 3
 FRAME_SLOTS = 4
 
 

@@ -26,19 +26,15 @@ def _ref_files():
     return os.path.join(GOLDEN, "two_cubes_432.dat")
 
 
-# cells_indexed: the cell-binned variant sharded runs use (state in particle order, cell-ordered
-# copy of the positions, index list of the owned particles), exercised here on one GPU
-ALGOS = ["allpairs", "cells", "cells_indexed"]
+ALGOS = ["allpairs", "cells"]
 
 
 def _select(psim, sim, algo):
-    if algo == "cells_indexed":
-        sim.set_option(psim.OPT_CELLS_INDEXED, 1)
     sim.set_option(psim.OPT_FORCE_ALGO, psim.FORCE_ALL_PAIRS if algo == "allpairs" else psim.FORCE_CELL_BINNED)
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "cells", "cells_indexed"])
+@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "cells"])
 def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     ids, pos, vel = two_cubes()
     p = psim.make_params()

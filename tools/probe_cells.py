@@ -16,3 +16,7 @@ sim.advance(30 if algo == "cells" else 3)
 ms = sim.advance_timed(steps) / steps
 c = sim.counters()
 print(f"{algo} n={n} f{prec*8} ms/step={ms:.4f} steps/s={1e3/ms:.1f} pairs/s={n*(n-1)/ms*1e3:.3e} rebuilds={c.rebuilds}")
+sim.set_option(P.OPT_KERNEL_TIMING, 1)
+k0 = sim.counters(); ms2 = sim.advance_timed(steps) / steps; k1 = sim.counters()
+fk = (k1.force_ms - k0.force_ms) / max(1, k1.force_timed - k0.force_timed)
+print(f"   with per-launch events: ms/step={ms2:.4f} force kernel={fk:.4f} ms other={ms2-fk:.4f} ms launches/step={(k1.kernel_launches-k0.kernel_launches-1)/steps:.1f}")
