@@ -176,7 +176,7 @@ class SimT final : public psim_sim {
   CellPath<R> cells;
   // options
   int algo = PSIM_FORCE_ALL_PAIRS;
-  bool fused = true, timing = false, exact_diff = false;
+  bool fused = true, timing = false;
   // counters
   int64_t steps = 0, launches = 0, force_launches = 0, force_timed = 0;
   double force_ms = 0.0;

@@ -1,4 +1,4 @@
-"""Quick timing probe of one configuration: python tools/probe_cells.py N PRECISION [allpairs|cells] [steps]"""
+"""Quick timing probe of one configuration: python tools/probe.py N PRECISION [allpairs|cells] [steps]"""
 import os
 import sys
 
