@@ -342,7 +342,7 @@ class SimT final : public psim_sim {
           const int64_t waves = (ctas + slots - 1) / slots;
           double eff = (double)ctas / (double)(waves * slots);
           eff *= 1.0 - 0.015 * (8 - ri);                     // fewer i per lane: a little less efficient
-          if (w > 4) eff *= 0.99;
+          if (w == 8) eff *= 1.03;                           // measured: two 8-warp blocks per SM run a little denser
           if (S > 1) eff *= 0.95 - 0.03 * (S - 1);           // measured cost of cluster scheduling
           if (eff > best_eff) { best_eff = eff; best = {ri, w, S}; }
         }
