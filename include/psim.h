@@ -77,7 +77,8 @@ typedef enum psim_option {
                                     norm-expansion pre-filter (3 FMAs per ordered pair); 1 first-generation
                                     kernel with the distance test in difference form (3 sub, 1 mul, 2 FMA,
                                     1 compare per pair: the literal reading of stoermer:117-121);
-                                    2 first-generation kernel with the pre-filter */
+                                    2 first-generation kernel with the pre-filter; 3 distance filter on the
+                                    tensor cores (tcgen05.mma kind::tf32 with split operands, TMEM accumulator) */
 } psim_option;
 
 typedef struct psim_counters {

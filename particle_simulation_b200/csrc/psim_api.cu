@@ -21,6 +21,7 @@
 
 #include "psim_allpairs.cuh"
 #include "psim_allpairs2.cuh"
+#include "psim_allpairs_tc.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -256,7 +257,7 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMalloc(&pos[0], rec)); PSIM_CK(cudaMalloc(&pos[1], rec));
     PSIM_CK(cudaMalloc(&vel, rec)); PSIM_CK(cudaMalloc(&f_old, rec));
     PSIM_CK(cudaMalloc(&f_new, rec)); PSIM_CK(cudaMalloc(&disp, rec));
-    top2_cap = std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 32 * 6) * MAX_CLUSTER) + 8;
+    top2_cap = std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 32 * 6) * MAX_CLUSTER) + 8;   // most blocks any drift-producing kernel launches
     PSIM_CK(cudaMalloc(&top2_part, sizeof(R) * 2 * top2_cap));
     PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * world));
     PSIM_CK(cudaMalloc(&ctrl, sizeof(Control)));
@@ -384,6 +385,19 @@ class SimT final : public psim_sim {
 
   template <int MODE>
   psim_status launch_allpairs(const StepArgs<R>& a, int64_t* grid_out) {
+    if (variant == 3) {          // distance filter on the tensor cores (tcgen05 + TMEM)
+      *grid_out = blocks(i_hi - i_lo, tc::M);
+      // a block allocates all 512 TMEM columns: ask for enough (unused) dynamic shared memory that
+      // only one block fits on an SM, so no second block ever waits inside tcgen05.alloc
+      constexpr int kPad = 120 * 1024;
+      static bool attr_set[64] = {false};
+      if (!attr_set[device & 63]) {
+        PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tc_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPad));
+        attr_set[device & 63] = true;
+      }
+      tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::T, kPad, stream>>>(a);
+      return PSIM_OK;
+    }
     if (variant != 0) {
       *grid_out = blocks(i_hi - i_lo, T * RI);
       launch_v1<MODE>(a, *grid_out);
@@ -609,7 +623,7 @@ class SimT final : public psim_sim {
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER:
-        if (value < 0 || value > 2) return PSIM_ERR_INVALID_ARGUMENT;
+        if (value < 0 || value > 3) return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
     }

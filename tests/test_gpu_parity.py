@@ -34,7 +34,7 @@ def _select(psim, sim, algo):
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "cells"])
+@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "allpairs_tensor", "cells"])
 def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     ids, pos, vel = two_cubes()
     p = psim.make_params()
@@ -47,6 +47,9 @@ def test_initial_forces_match_oracle(psim, oracle, precision, variant):
         sim.set_positions(pos)
     elif variant == "allpairs_v1_filter":
         sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 2)
+        sim.set_positions(pos)
+    elif variant == "allpairs_tensor":
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 3)
         sim.set_positions(pos)
     elif variant.startswith("cells"):
         _select(psim, sim, variant)

@@ -12,6 +12,9 @@ steps = int(sys.argv[4]) if len(sys.argv) > 4 and sys.argv[4].isdigit() else 100
 ids, pos, vel, area = G.synthetic(n)
 sim = P.Simulation(P.make_params(length_of_area=area), ids, pos, vel, prec)
 sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED if algo == "cells" else P.FORCE_ALL_PAIRS)
+if algo.startswith("allpairs") and algo[-1].isdigit():
+    sim.set_option(P.OPT_EXACT_DIFF_FILTER, int(algo[-1]))      # allpairs1/2/3: kernel variants
+    sim.set_positions(pos.astype(P.native.rt(prec)))
 sim.advance(30 if algo == "cells" else 3)
 ms = sim.advance_timed(steps) / steps
 c = sim.counters()
