@@ -22,6 +22,7 @@
 #include "psim_allpairs.cuh"
 #include "psim_allpairs2.cuh"
 #include "psim_allpairs_tc.cuh"
+#include "psim_allpairs_tc2.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -174,6 +175,7 @@ class SimT final : public psim_sim {
   std::vector<int32_t> ids;
   R* tmp3 = nullptr;            // [3 * n_pad] scratch for pack/unpack
   unsigned char* tmp_active = nullptr;
+  unsigned char* tc_bops = nullptr;     // tensor-core variant: B operand tiles of all particles
   CellPath<R> cells;
   // options
   int algo = PSIM_FORCE_ALL_PAIRS;
@@ -208,7 +210,8 @@ class SimT final : public psim_sim {
     for (auto& e : ev_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     ev_pool.clear();
     cudaFree(pos[0]); cudaFree(pos[1]); cudaFree(vel); cudaFree(f_old); cudaFree(f_new); cudaFree(disp);
-    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active);
+    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active); cudaFree(tc_bops);
+    tc_bops = nullptr;
     pos[0] = pos[1] = vel = f_old = f_new = disp = nullptr;
     top2_part = top2_rank = nullptr; ctrl = nullptr; tmp3 = nullptr; tmp_active = nullptr;
     if (stream) cudaStreamDestroy(stream);
@@ -385,10 +388,24 @@ class SimT final : public psim_sim {
 
   template <int MODE>
   psim_status launch_allpairs(const StepArgs<R>& a, int64_t* grid_out) {
-    if (variant == 3) {          // distance filter on the tensor cores (tcgen05 + TMEM)
+    if (variant == 3) {          // distance filter on the tensor cores (tcgen05 + TMEM), warp-specialised
       *grid_out = blocks(i_hi - i_lo, tc::M);
-      // a block allocates all 512 TMEM columns: ask for enough (unused) dynamic shared memory that
-      // only one block fits on an SM, so no second block ever waits inside tcgen05.alloc
+      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
+      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c);
+      ++launches;
+      // ring of B tiles + candidate queues (128 KB): also guarantees ONE block per SM — a block
+      // allocates all 512 TMEM columns, and no second block should ever wait inside tcgen05.alloc
+      constexpr int kSmem = tc::SMEM_BYTES;
+      static bool attr_set[64] = {false};
+      if (!attr_set[device & 63]) {
+        PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tcws_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_set[device & 63] = true;
+      }
+      tc::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops);
+      return PSIM_OK;
+    }
+    if (variant == 4) {          // first, lock-step tensor-core version (kept for comparison)
+      *grid_out = blocks(i_hi - i_lo, tc::M);
       constexpr int kPad = 120 * 1024;
       static bool attr_set[64] = {false};
       if (!attr_set[device & 63]) {
@@ -623,7 +640,7 @@ class SimT final : public psim_sim {
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER:
-        if (value < 0 || value > 3) return PSIM_ERR_INVALID_ARGUMENT;
+        if (value < 0 || value > 4) return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
     }
