@@ -89,6 +89,10 @@ typedef struct psim_counters {
   double  force_ms;         /* summed device time of timed force launches (PSIM_OPT_KERNEL_TIMING) */
   int64_t force_timed;      /* number of force launches that were timed */
   int64_t n_active;         /* active particles after the last completed step */
+  int64_t filter_pairs;     /* ordered in-range pairs (i, j) of this handle's i-slice that the last force launch
+                             * sent through its exact path; tracked by the tensor-core all-pairs kernel only
+                             * (-1 otherwise).  Equal to psim_count_pairs_in_range at the same positions iff
+                             * the distance filter dropped no pair: the conservativeness check of the tests. */
 } psim_counters;
 
 typedef struct psim_sim psim_sim;   /* opaque */

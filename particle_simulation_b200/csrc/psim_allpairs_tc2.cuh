@@ -24,21 +24,23 @@ namespace tc {
 constexpr int N2 = 128;                         // j records per tile of this kernel = accumulator columns per buffer
 constexpr int NBUF = 512 / N2;                  // TMEM ring: four accumulators of 128 columns
 constexpr int NCTL = NBUF;                      // MMA warps: warp w owns accumulator w, tiles t = w (mod NCTL)
-constexpr int NPAIR = 6;                        // shared-memory ring: 6 slots of two tiles (one 16 KB bulk copy each)
-constexpr int STAGES = 2 * NPAIR;               // 12 x 8 KB
+constexpr int NPAIR = 4;                        // shared-memory ring: 4 slots of two tiles (one 16 KB bulk copy each)
+constexpr int STAGES = 2 * NPAIR;               // 8 x 8 KB
 constexpr int TILE_BYTES = N2 * K * 4;          // 8 KB
 constexpr int NQ = 4;                           // column groups: warp w reads TMEM lanes 32 (w % 4).., columns 32 (w / 4)..
 constexpr int CW = 4 * NQ;                      // consumer warps
 constexpr int TW = 32 * (CW + NCTL + 1);        // + the MMA warps + the TMA producer warp
-constexpr int QC = 32;                          // candidate queue entries per consumer thread (64 KB in all)
+constexpr int QC = 48;                          // candidate queue entries per consumer thread (96 KB in all)
 constexpr int RING_BYTES = STAGES * TILE_BYTES;
 constexpr int SMEM_BYTES = RING_BYTES + QC * 32 * CW * 4;
 
 // B operand rows of all particles, tile by tile, in the canonical layout of chunk_off().
 template <class R>
 __global__ void __launch_bounds__(256)
-tc_prepare_kernel(const Real4<R>* __restrict__ pos, unsigned char* __restrict__ bops, int64_t n_pad, Consts<R> c) {
+tc_prepare_kernel(const Real4<R>* __restrict__ pos, unsigned char* __restrict__ bops, int64_t n_pad, Consts<R> c,
+                  unsigned long long* __restrict__ pair_count) {
   const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (j == 0) *pair_count = 0ull;                  // the force kernel that follows counts what its exact path evaluates
   if (j >= n_pad) return;
   const FilterRec f = filter_record_tc(pos[j], c, (float)c.r_cut);
   float x1, x2, y1, y2, z1, z2, w1, w2, w3;
@@ -95,7 +97,8 @@ __device__ __forceinline__ void mbar_spin(unsigned addr, unsigned parity) {
 #endif
 
 template <class R>
-__device__ __noinline__ void flush_queue(const Real4<R>* __restrict__ pos, const Consts<R>& c, int64_t ig, const int* q, int cnt, R* f) {
+__device__ __noinline__ void flush_queue(const Real4<R>* __restrict__ pos, const Consts<R>& c, int64_t ig, const int* q, int cnt, R* f,
+                                         unsigned* in_range) {
   if (cnt == 0) return;                            // rows past i_hi / inactive rows never queue anything
   const Real4<R> pi = pos[ig];
   for (int e = 0; e < cnt; ++e) {
@@ -105,7 +108,10 @@ __device__ __noinline__ void flush_queue(const Real4<R>* __restrict__ pos, const
     if (pj.w >= c.huge) continue;
     const R dx = r_sub(pi.x, pj.x), dy = r_sub(pi.y, pj.y), dz = r_sub(pi.z, pj.z);
     const R r2 = r_add(r_add(r_mul(dx, dx), r_mul(dy, dy)), r_mul(dz, dz));
-    if (r2 < c.cut2_pad) pair_force(pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, c, f[0], f[1], f[2]);
+    if (r2 < c.cut2_pad) {
+      pair_force(pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, c, f[0], f[1], f[2]);
+      if (r_sqrt(r2) < c.r_cut) ++*in_range;       // the predicate of count_pairs_kernel (psim_allpairs.cuh)
+    }
   }
 }
 
@@ -113,8 +119,8 @@ __device__ __forceinline__ float min3f(float a, float b, float c) { return fminf
 
 // 32 columns of this thread's row: 16 three-input minima (groups of 9, 9, 9 and 5 columns), one compare;
 // the rare hit descends to the groups and pushes the candidate columns.
-template <class R, class Flush>
-__device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], float cut, int j0, int* q, int& cnt, Flush&& flush) {
+template <class R>
+__device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], float cut, int j0, int* q, int& cnt) {
   float mg[4];
 #pragma unroll
   for (int g = 0; g < 3; ++g) {
@@ -125,7 +131,7 @@ __device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], float cut, 
   mg[3] = min3f(min3f(__uint_as_float(r[27]), __uint_as_float(r[28]), __uint_as_float(r[29])), __uint_as_float(r[30]),
                 __uint_as_float(r[31]));
   const float m = fminf(min3f(mg[0], mg[1], mg[2]), mg[3]);
-  if (m < cut) {
+  if (m < cut) {                                   // the caller guarantees 32 free queue entries
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       if (mg[g] < cut) {
@@ -134,7 +140,7 @@ __device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], float cut, 
           const int u = 9 * g + k;                 // static after unrolling: r[] must stay in registers
           if (u < 32 && __uint_as_float(r[u < 32 ? u : 0]) < cut) {
             q[cnt * (32 * CW)] = j0 + u;
-            if (++cnt == QC) flush();
+            ++cnt;
           }
         }
       }
@@ -151,7 +157,7 @@ __device__ long long g_trace[40][512];
 
 template <class R, int MODE>
 __global__ void __launch_bounds__(TW, 1)
-allpairs_tcws_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops) {
+allpairs_tcws_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, unsigned long long* __restrict__ pair_count) {
   extern __shared__ __align__(1024) unsigned char sB[];          // STAGES x 16 KB ring (+ padding, see launch)
   __shared__ __align__(128) unsigned char sA[M * K * 4];          // 8 KB
   __shared__ __align__(8) unsigned long long b_full[NPAIR], b_empty[NPAIR], d_full[NBUF], d_empty[NBUF];
@@ -201,6 +207,7 @@ allpairs_tcws_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
   const unsigned tm = tmem_base_s;
 
   R f[3] = {(R)0, (R)0, (R)0};
+  unsigned in_range = 0;                           // ordered in-range pairs this thread's exact path evaluated
   if (warp == CW + NCTL) {
     if (lane == 0) {
       // ===== TMA producer: one 16 KB bulk copy per pair of tiles, as far ahead as the ring allows =====
@@ -264,7 +271,7 @@ allpairs_tcws_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
     constexpr int COLS = N2 / NQ;                  // 32 columns = one load per tile
     int* q = reinterpret_cast<int*>(sB + RING_BYTES) + tid;      // this thread's queue: entry e at q[e * 32 CW]
     int cnt = 0;
-    auto flush = [&]() { flush_queue<R>(a.pos_cur, c, ig, q, cnt, f); cnt = 0; };
+    auto flush = [&]() { flush_queue<R>(a.pos_cur, c, ig, q, cnt, f, &in_range); cnt = 0; };
     const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(half * COLS);
     const unsigned dfull0 = pinned(smem_u32(&d_full[0])), dempty0 = pinned(smem_u32(&d_empty[0]));
     const int jbase = half * COLS;
@@ -277,26 +284,33 @@ allpairs_tcws_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
 #else
 #define PT(acc) {}
 #endif
-    for (int t = 0; t < nt; ++t) {
-      const int buf = t & (NBUF - 1);
-      PSIM_MBAR_WAIT(dfull0 + 8u * buf, (unsigned)((t / NBUF) & 1));   // (polling with one lane + __syncwarp: slower, measured)
-      PT(c_wait) if (lane == 0) TR(8 + 2 * warp, t)
-      asm volatile("tcgen05.fence::after_thread_sync;");
-      unsigned r0[32];
-      PSIM_TMEM_LD32(r0, lane_base + (unsigned)(buf * N2));
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      asm volatile("tcgen05.fence::before_thread_sync;");       // data is in registers: hand the buffer back
-      __syncwarp();
-      if (lane == 0) mbar_arrive(dempty0 + 8u * buf);
-      PT(c_ld) if (lane == 0) TR(9 + 2 * warp, t)
-      queue_chunk<R>(r0, cut, t * N2 + jbase, q, cnt, flush);
-      PT(c_q)
+    for (int t0 = 0; t0 < nt; t0 += NBUF) {        // nt is a multiple of 8 (n_pad is a multiple of 1024)
+      const unsigned par = (unsigned)((t0 / NBUF) & 1);
+#pragma unroll
+      for (int buf = 0; buf < NBUF; ++buf) {
+        const int t = t0 + buf;
+        PSIM_MBAR_WAIT(dfull0 + 8u * buf, par);    // (polling with one lane + __syncwarp: slower, measured)
+        PT(c_wait) if (lane == 0) TR(8 + 2 * warp, t)
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        unsigned r0[32];
+        PSIM_TMEM_LD32(r0, lane_base + (unsigned)(buf * N2));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;");     // data is in registers: hand the buffer back
+        __syncwarp();
+        if (lane == 0) mbar_arrive(dempty0 + 8u * buf);
+        PT(c_ld) if (lane == 0) TR(9 + 2 * warp, t)
+        queue_chunk<R>(r0, cut, t * N2 + jbase, q, cnt);
+        if (cnt > QC - 32) flush();                // rare; the 32 values are dead here, nothing to save around the call
+        PT(c_q)
+      }
     }
 #ifdef PSIM_TC_PROF
     if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 15)) printf("consumer %d per tile: wait %lld ld %lld queue %lld\n", warp, c_wait / nt, c_ld / nt, c_q / nt);
 #endif
 #undef PT
     flush();                                       // the exact path, once the pipeline is done
+    for (int off = 16; off > 0; off >>= 1) in_range += __shfl_xor_sync(0xffffffffu, in_range, off);
+    if (lane == 0 && in_range) atomicAdd(pair_count, (unsigned long long)in_range);
   }
 
   // --- the column groups of a row meet (fixed order); epilogue by the thread of group 0 ---

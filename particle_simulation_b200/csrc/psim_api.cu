@@ -176,6 +176,7 @@ class SimT final : public psim_sim {
   R* tmp3 = nullptr;            // [3 * n_pad] scratch for pack/unpack
   unsigned char* tmp_active = nullptr;
   unsigned char* tc_bops = nullptr;     // tensor-core variant: B operand tiles of all particles
+  unsigned long long* tc_pairs = nullptr;  // ... and the in-range pair count of its last launch (psim_counters.filter_pairs)
   CellPath<R> cells;
   // options
   int algo = PSIM_FORCE_ALL_PAIRS;
@@ -210,8 +211,8 @@ class SimT final : public psim_sim {
     for (auto& e : ev_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     ev_pool.clear();
     cudaFree(pos[0]); cudaFree(pos[1]); cudaFree(vel); cudaFree(f_old); cudaFree(f_new); cudaFree(disp);
-    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active); cudaFree(tc_bops);
-    tc_bops = nullptr;
+    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active); cudaFree(tc_bops); cudaFree(tc_pairs);
+    tc_bops = nullptr; tc_pairs = nullptr;
     pos[0] = pos[1] = vel = f_old = f_new = disp = nullptr;
     top2_part = top2_rank = nullptr; ctrl = nullptr; tmp3 = nullptr; tmp_active = nullptr;
     if (stream) cudaStreamDestroy(stream);
@@ -391,7 +392,8 @@ class SimT final : public psim_sim {
     if (variant == 3) {          // distance filter on the tensor cores (tcgen05 + TMEM), warp-specialised
       *grid_out = blocks(i_hi - i_lo, tc::M);
       if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
-      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c);
+      if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
+      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, tc_pairs);
       ++launches;
       // ring of B tiles + candidate queues (128 KB): also guarantees ONE block per SM — a block
       // allocates all 512 TMEM columns, and no second block should ever wait inside tcgen05.alloc
@@ -401,7 +403,7 @@ class SimT final : public psim_sim {
         PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tcws_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
         attr_set[device & 63] = true;
       }
-      tc::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops);
+      tc::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs);
       return PSIM_OK;
     }
     if (variant == 4) {          // first, lock-step tensor-core version (kept for comparison)
@@ -621,7 +623,11 @@ class SimT final : public psim_sim {
     pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nullptr, pos[cur], nullptr, n, c, ctrl); ++launches;
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
+    unsigned long long fp = 0;
+    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && variant == 3 && tc_pairs;
+    if (tracked) PSIM_CK(cudaMemcpyAsync(&fp, tc_pairs, sizeof fp, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
+    out->filter_pairs = tracked ? (int64_t)fp : -1;
     out->steps = steps;
     out->rebuilds = (int64_t)h.rebuilds;
     out->kernel_launches = launches + cells.launches;

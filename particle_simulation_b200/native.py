@@ -51,6 +51,7 @@ class Counters(C.Structure):
         ("force_ms", C.c_double),
         ("force_timed", C.c_int64),
         ("n_active", C.c_int64),
+        ("filter_pairs", C.c_int64),
     ]
 
 

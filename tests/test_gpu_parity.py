@@ -149,3 +149,41 @@ def test_conservation_and_energy(psim, oracle, algo):
     assert np.abs(p1 - p0).max() <= 1e-9 * np.abs(p0).max()          # momentum: pairwise antisymmetric forces
     assert abs((k1 + u1) - (k0 + u0)) <= 2e-5 * abs(k0 + u0)          # velocity Verlet, dt = 1e-3
     sim.close()
+
+
+@pytest.mark.parametrize("precision", [4, 8])
+@pytest.mark.parametrize("case", ["lattice_65536", "hot_gas_32768", "two_cubes"])
+def test_tensor_core_filter_drops_no_pair(psim, precision, case):
+    """The tensor-core distance filter (split-TF32 Gram matrix) must be conservative: the ordered in-range
+    pairs its exact path evaluated (psim_counters.filter_pairs) equal the exact O(N^2) count, and stay equal
+    while the configuration moves.  The forces then agree with the default kernel's up to summation order
+    (both evaluate every pair with the same one-rounding-per-operation arithmetic)."""
+    from particle_simulation_b200 import generate as G
+    if case == "two_cubes":
+        ids, pos, vel = two_cubes()
+        params = psim.make_params()
+    elif case == "lattice_65536":
+        ids, pos, vel, area = G.synthetic(65536)
+        params = psim.make_params(length_of_area=area)
+    else:   # strongly perturbed lattice: many pairs close to the cut-off on both sides
+        ids, pos, vel, area = G.synthetic(32768, thermal=0.1)
+        rng = np.random.default_rng(11)
+        pos = pos + rng.uniform(-0.45, 0.45, pos.shape)
+        vel = vel * 0.0
+        params = psim.make_params(length_of_area=area, delta_t=1e-5)
+    ref = psim.Simulation(params, ids, pos, vel, precision)
+    sim = psim.Simulation(params, ids, pos, vel, precision)
+    sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 3)
+    sim.set_positions(pos)
+    for round_ in range(3):
+        exact = sim.pairs_in_range()
+        assert exact > 0
+        assert sim.counters().filter_pairs == exact
+        assert ref.counters().filter_pairs == -1
+        f, f_ref = sim.forces(), ref.forces()
+        scale = np.abs(f_ref).max()
+        assert np.abs(f - f_ref).max() <= (1e-4 if precision == 4 else 1e-11) * scale
+        sim.advance(7)
+        ref.advance(7)
+    sim.close()
+    ref.close()
