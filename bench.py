@@ -58,6 +58,8 @@ def parse_args():
     ap.add_argument("--no-cells", action="store_true", help="skip the cell-binned companion measurement")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--exact-diff", action="store_true", help="difference-form distance test (no pre-filter)")
+    ap.add_argument("--ffma2", action="store_true", help="all-pairs on the CUDA cores only (packed-FP32 filter kernel) "
+                    "instead of the default tensor-core filter kernel")
     return ap.parse_args()
 
 
@@ -251,8 +253,8 @@ def main():
     sim = P.Simulation(params, ids, pos, vel, prec, device=local_rank, rank=rank, world=world, nccl_unique_id=uid)
     if args.algo == "cells":
         sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
-    if args.exact_diff:
-        sim.set_option(P.OPT_EXACT_DIFF_FILTER, 1)
+    if args.exact_diff or args.ffma2:
+        sim.set_option(P.OPT_EXACT_DIFF_FILTER, 1 if args.exact_diff else 5)
         sim.set_positions(pos.astype(native.rt(prec)))
     pairs_total = float(n) * (n - 1)
     n_own = sim.i_hi - sim.i_lo
@@ -285,12 +287,15 @@ def main():
     achieved = flops_launch / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else 0.0
     peak64, _ = native.measure_fma_peak(8, local_rank)
     peak32, _ = native.measure_fma_peak(4, local_rank)
-    # Which pipe bounds the kernel.  The production all-pairs kernel runs its distance tests as
-    # packed FP32 FMAs for BOTH working precisions (exact path in the working precision), so it is
-    # bound by the FP32 FMA pipe; the first-generation difference-form kernel (--exact-diff) and the
-    # cell-binned kernel in f64 spend their time on the FP64 pipe.
+    # Which unit bounds the kernel.
+    #  * default all-pairs kernel (allpairs_tcws_kernel): the distance test of every ordered pair is one entry of a
+    #    Gram matrix computed by tcgen05.mma kind::tf32 on split operands (K = 16: 32 tensor flops per pair); the
+    #    CUDA cores only take minima over 32-column chunks and evaluate the few pairs that pass -> bound "tensor".
+    #    Peak: MEASURED_PEAKS.json's dense bf16 figure / 2 (kind::tf32 runs at half the bf16 rate).
+    #  * --ffma2: the same filter as packed FP32 FMAs for both working precisions -> FP32 FMA pipe.
+    #  * --exact-diff and the cell-binned kernel in f64 -> FP64 FMA pipe.
+    tensor = args.algo == "allpairs" and not args.exact_diff and not args.ffma2
     fp32_bound = (prec == 4) or (args.algo == "allpairs" and not args.exact_diff)
-    peak = peak32 if fp32_bound else peak64
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
@@ -298,25 +303,58 @@ def main():
     except Exception:
         pass
     bytes_launch = n_own * (4 * prec) * 6.0 + n * 4 * prec    # owned records r/w + one pass over all positions
-    executed = 6.0 * n_own * (n - 1) / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 and args.algo == "allpairs" else None
-    roofline = {
-        "bound": "fp32_fma" if fp32_bound else "fp64_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-        "frac": achieved / peak if peak else None, "traffic": traffic,
-        "peak_source": "psim_measure_fma_peak: dependent-free FMA loop on all SMs, this run (of measured; "
-                       "MEASURED_PEAKS.json has no vector-FMA figure)",
-        "kernel": ("allpairs_warp_kernel" if not args.exact_diff else "allpairs_step_kernel") if args.algo == "allpairs" else "cell_force_kernel",
-        "kernel_ms": kernel_ms, "launches_timed": int(n_timed), "flops_per_launch": flops_launch,
-        "flops_accounting": "SURVEY.md 8(d): 8 per ordered pair tested + 15 per ordered pair in range",
-        "pairs_in_range_per_step": int(sum_over_ranks(pin_own)),
-        "share_of_step": kernel_ms / (ms / args.steps) if ms > 0 else None,
-        "hbm_bytes_per_launch_algorithmic": bytes_launch,
-        "fp64_fma_peak": peak64, "fp32_fma_peak": peak32,
-        "frac_of_fp64_fma_peak": achieved / peak64 if peak64 else None,
-        "executed_filter_tflops": executed,
-        "executed_frac": (executed / peak) if (executed and peak) else None,
-        "note": "frac uses the survey's 8-flop difference-form count per pair; the kernel's norm-expansion filter "
-                "executes 3 FMAs = 6 flops per pair (executed_*), on the FP32 pipe, so frac_of_fp64_fma_peak can exceed 1",
-    }
+    survey_tflops = achieved
+    if tensor:
+        peaks, peak_src = None, "fallback of B200_PROFILING.md (1590 TFLOP/s dense bf16) / 2 for kind::tf32"
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+            peak_src = "MEASURED_PEAKS.json bf16_tflops (burst; the kernel is timed alone) / 2 for kind::tf32"
+        except Exception:
+            pass
+        peak = 0.5 * (peaks["bf16_tflops"] if peaks else 1590.0)
+        n_pad_cols = ((n + 1023) // 1024) * 1024
+        tensor_flops = 32.0 * n_own * n_pad_cols          # 2 * K flops per accumulator entry, K = 16
+        achieved = tensor_flops / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else 0.0
+        roofline = {
+            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": achieved / peak if peak else None, "traffic": traffic, "peak_source": peak_src,
+            "kernel": "allpairs_tcws_kernel", "kernel_ms": kernel_ms, "launches_timed": int(n_timed),
+            "flops_per_launch": tensor_flops,
+            "flops_accounting": "tensor pipe: 2*K = 32 flops per ordered pair tested (split-TF32 Gram matrix, K = 16); "
+                                "SURVEY.md 8(d)'s CUDA-core accounting (8 per pair tested + 15 per pair in range) is "
+                                "reported as survey_tflops",
+            "survey_flops_per_launch": flops_launch, "survey_tflops": survey_tflops,
+            "survey_frac_of_fp32_fma_peak": survey_tflops / peak32 if peak32 else None,
+            "survey_frac_of_fp64_fma_peak": survey_tflops / peak64 if peak64 else None,
+            "pairs_in_range_per_step": int(sum_over_ranks(pin_own)),
+            "filter_pairs_per_step": int(sum_over_ranks(k1.filter_pairs)) if k1.filter_pairs >= 0 else None,
+            "share_of_step": kernel_ms / (ms / args.steps) if ms > 0 else None,
+            "hbm_bytes_per_launch_algorithmic": bytes_launch,
+            "fp64_fma_peak": peak64, "fp32_fma_peak": peak32,
+            "note": "the survey-accounting rate can exceed the FP32 FMA peak because the pair tests run on the tensor pipe",
+        }
+    else:
+        peak = peak32 if fp32_bound else peak64
+        executed = 6.0 * n_own * (n - 1) / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 and args.algo == "allpairs" else None
+        roofline = {
+            "bound": "fp32_fma" if fp32_bound else "fp64_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": achieved / peak if peak else None, "traffic": traffic,
+            "peak_source": "psim_measure_fma_peak: dependent-free FMA loop on all SMs, this run (of measured; "
+                           "MEASURED_PEAKS.json has no vector-FMA figure)",
+            "kernel": ("allpairs_warp_kernel" if not args.exact_diff else "allpairs_step_kernel") if args.algo == "allpairs" else "cell_force_kernel",
+            "kernel_ms": kernel_ms, "launches_timed": int(n_timed), "flops_per_launch": flops_launch,
+            "flops_accounting": "SURVEY.md 8(d): 8 per ordered pair tested + 15 per ordered pair in range",
+            "pairs_in_range_per_step": int(sum_over_ranks(pin_own)),
+            "share_of_step": kernel_ms / (ms / args.steps) if ms > 0 else None,
+            "hbm_bytes_per_launch_algorithmic": bytes_launch,
+            "fp64_fma_peak": peak64, "fp32_fma_peak": peak32,
+            "frac_of_fp64_fma_peak": achieved / peak64 if peak64 else None,
+            "executed_filter_tflops": executed,
+            "executed_frac": (executed / peak) if (executed and peak) else None,
+            "note": "frac uses the survey's 8-flop difference-form count per pair; the kernel's norm-expansion filter "
+                    "executes 3 FMAs = 6 flops per pair (executed_*), on the FP32 pipe, so frac_of_fp64_fma_peak can exceed 1",
+        }
 
     # ---- e2e: the force operator with host buffers through the C ABI ----
     rt = native.rt(prec)
@@ -348,7 +386,7 @@ def main():
         "config": {"workload": workload_name(n, area), "n_particles": n, "algo": args.algo,
                    "parallelism": "i-sharded x%d, position all-gather per step" % world if world > 1 else "single GPU",
                    "l2": "not flushed between steps: every step reads the positions the previous step wrote "
-                         "(state is carried on the device, %.0f MB working set); the kernel is FMA-pipe bound" %
+                         "(state is carried on the device, %.0f MB working set); the force kernel is compute bound (see roofline.bound)" %
                          (n * 4 * prec * 6 / 1e6)},
         "roofline": roofline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }

@@ -73,12 +73,19 @@ typedef enum psim_option {
   PSIM_OPT_FORCE_ALGO = 0,      /* psim_force_algo */
   PSIM_OPT_FUSED_STEP = 1,      /* 1: force+kick+drift in one kernel (default), 0: separate kernels */
   PSIM_OPT_KERNEL_TIMING = 2,   /* 1: bracket every force-kernel launch with CUDA events */
-  PSIM_OPT_EXACT_DIFF_FILTER = 3, /* all-pairs kernel variant: 0 (default) warp-autonomous kernel with the
-                                    norm-expansion pre-filter (3 FMAs per ordered pair); 1 first-generation
-                                    kernel with the distance test in difference form (3 sub, 1 mul, 2 FMA,
-                                    1 compare per pair: the literal reading of stoermer:117-121);
-                                    2 first-generation kernel with the pre-filter; 3 distance filter on the
-                                    tensor cores (tcgen05.mma kind::tf32 with split operands, TMEM accumulator) */
+  PSIM_OPT_EXACT_DIFF_FILTER = 3, /* all-pairs kernel variant.
+                                    0 (default) and 3: distance filter on the tensor cores (tcgen05.mma kind::tf32
+                                      on split operands, TMEM accumulators, TMA-fed), exact pair arithmetic on the
+                                      CUDA cores for the few pairs that pass;
+                                    5: warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in
+                                      packed FP32 (3 FMAs per ordered pair) - the default before the tensor-core
+                                      kernel, 1.35-3x slower;
+                                    1: first-generation kernel with the distance test in difference form (3 sub,
+                                      1 mul, 2 FMA, 1 compare per pair: the literal reading of stoermer:117-121);
+                                    2: first-generation kernel with the pre-filter;
+                                    4: first, lock-step tensor-core kernel (kept for comparison).
+                                    All variants evaluate the same pairs with the same arithmetic; results differ
+                                    by summation order only. */
 } psim_option;
 
 typedef struct psim_counters {

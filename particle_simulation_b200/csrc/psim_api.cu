@@ -151,7 +151,7 @@ class SimT final : public psim_sim {
   static constexpr int RI = 2;                                    // i-particles per thread
   static constexpr int TS = 256;                                  // threads of the streaming kernels
   static constexpr int MAX_CLUSTER = 8;                           // portable cluster size limit
-  int variant = 0;      // 0: cluster kernel (default), 1: difference-form v1 kernel, 2: pre-filter v1 kernel
+  int variant = 0;      // 0 / 3: tensor-core filter kernel (default), 5: FFMA2 warp kernel, 1 / 2: v1 kernels, 4: lock-step tensor-core kernel
   int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
   int warps_forced = 0;
@@ -389,7 +389,7 @@ class SimT final : public psim_sim {
 
   template <int MODE>
   psim_status launch_allpairs(const StepArgs<R>& a, int64_t* grid_out) {
-    if (variant == 3) {          // distance filter on the tensor cores (tcgen05 + TMEM), warp-specialised
+    if (variant == 0 || variant == 3) {   // distance filter on the tensor cores (tcgen05 + TMEM), warp-specialised: the default
       *grid_out = blocks(i_hi - i_lo, tc::M);
       if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
       if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
@@ -417,7 +417,7 @@ class SimT final : public psim_sim {
       tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::T, kPad, stream>>>(a);
       return PSIM_OK;
     }
-    if (variant != 0) {
+    if (variant != 5) {
       *grid_out = blocks(i_hi - i_lo, T * RI);
       launch_v1<MODE>(a, *grid_out);
       return PSIM_OK;
@@ -624,7 +624,7 @@ class SimT final : public psim_sim {
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
     unsigned long long fp = 0;
-    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && variant == 3 && tc_pairs;
+    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && (variant == 0 || variant == 3) && tc_pairs;
     if (tracked) PSIM_CK(cudaMemcpyAsync(&fp, tc_pairs, sizeof fp, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     out->filter_pairs = tracked ? (int64_t)fp : -1;
@@ -646,7 +646,7 @@ class SimT final : public psim_sim {
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER:
-        if (value < 0 || value > 4) return PSIM_ERR_INVALID_ARGUMENT;
+        if (value < 0 || value > 5) return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
     }

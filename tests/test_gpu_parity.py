@@ -26,15 +26,17 @@ def _ref_files():
     return os.path.join(GOLDEN, "two_cubes_432.dat")
 
 
-ALGOS = ["allpairs", "cells"]
+ALGOS = ["allpairs", "allpairs_ffma2", "cells"]
 
 
 def _select(psim, sim, algo):
-    sim.set_option(psim.OPT_FORCE_ALGO, psim.FORCE_ALL_PAIRS if algo == "allpairs" else psim.FORCE_CELL_BINNED)
+    sim.set_option(psim.OPT_FORCE_ALGO, psim.FORCE_CELL_BINNED if algo == "cells" else psim.FORCE_ALL_PAIRS)
+    if algo == "allpairs_ffma2":
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "allpairs_tensor", "cells"])
+@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "allpairs_tensor", "allpairs_tensor_lockstep", "allpairs_ffma2", "cells"])
 def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     ids, pos, vel = two_cubes()
     p = psim.make_params()
@@ -48,8 +50,14 @@ def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     elif variant == "allpairs_v1_filter":
         sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 2)
         sim.set_positions(pos)
-    elif variant == "allpairs_tensor":
+    elif variant == "allpairs_tensor":                 # explicit; "allpairs" (value 0) selects the same kernel
         sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 3)
+        sim.set_positions(pos)
+    elif variant == "allpairs_tensor_lockstep":
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 4)
+        sim.set_positions(pos)
+    elif variant == "allpairs_ffma2":
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)
         sim.set_positions(pos)
     elif variant.startswith("cells"):
         _select(psim, sim, variant)
@@ -172,9 +180,9 @@ def test_tensor_core_filter_drops_no_pair(psim, precision, case):
         vel = vel * 0.0
         params = psim.make_params(length_of_area=area, delta_t=1e-5)
     ref = psim.Simulation(params, ids, pos, vel, precision)
-    sim = psim.Simulation(params, ids, pos, vel, precision)
-    sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 3)
-    sim.set_positions(pos)
+    ref.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)        # the CUDA-core kernel
+    ref.set_positions(pos)
+    sim = psim.Simulation(params, ids, pos, vel, precision)   # default: the tensor-core kernel
     for round_ in range(3):
         exact = sim.pairs_in_range()
         assert exact > 0
