@@ -181,7 +181,12 @@ psim_status psim_set_positions(psim_sim* sim, const void* pos, const uint8_t* ac
  * current (post-kick) state into pinned slot `slot` (0..PSIM_FRAME_SLOTS-1) by
  * async D2H on a side stream, without stalling the stepping stream; then wait
  * for a slot and get pointers into the pinned buffers (valid until the slot is
- * snapshotted again).  pos/vel point at `precision`-byte reals, packed xyz. */
+ * snapshotted again).  pos/vel point at `precision`-byte reals, packed xyz.
+ * psim_snapshot_wait is the one entry point that may be called from a second
+ * host thread while the owning thread keeps calling psim_advance /
+ * psim_snapshot_async on OTHER slots (simu_b200's writer thread does): it only
+ * reads the slot's event and pinned buffers.  The hand-over of the slot number
+ * between the threads must itself be synchronised by the host. */
 #define PSIM_FRAME_SLOTS 4
 psim_status psim_snapshot_async(psim_sim* sim, int slot);
 psim_status psim_snapshot_wait(psim_sim* sim, int slot, const int32_t** id,

@@ -1,7 +1,7 @@
 // simu_main.cpp — the reference's command line over the B200 library:
 //
 //   simu_b200 <parameter-file> <particle-file> <output-file> [--precision 4|8]
-//             [--algo cells|allpairs] [--device N] [--quiet]
+//             [--algo cells|allpairs] [--device N] [--quiet] [--sync-io]
 //
 // Follows program_particle_simulation_openmp.f08: exactly three positional
 // arguments (:146-154), namelist and particle file as read there (:180-286),
@@ -10,13 +10,22 @@
 // with stop_program (message, then a bare `stop`, i.e. exit status 0,
 // module_auxiliary_routines.f08:24-49) behave the same way here; failures of
 // the GPU library itself exit with status 2.
+//
+// Frames leave through a three-stage pipeline so that write_data (:327-365) never
+// holds up the stepping: the GPU keeps stepping, a side stream drains snapshot k
+// into one of PSIM_FRAME_SLOTS pinned slots, and a writer thread filters inactive
+// particles and appends frame k-1, k-2, ... to the file (--sync-io: no thread).
 #include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <fstream>
+#include <mutex>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "host_io.hpp"
@@ -40,11 +49,66 @@ static void gpu_check(psim_status st, const char* where) {
   std::exit(2);
 }
 
+// Writer thread of the frame pipeline.  The stepping thread hands over (slot, step) after
+// psim_snapshot_async; the writer blocks in psim_snapshot_wait (the only library call it makes: it
+// reads that slot's event and pinned buffers, nothing the stepping thread touches), writes the frame
+// and frees the slot.  Frames are written in hand-over order; a slot is reused only after the frame
+// that occupied it is on its way to the file (acquire()).
+class FramePipe {
+ public:
+  FramePipe(psim_sim* sim, FrameWriter* out, int64_t n, bool threaded) : sim_(sim), out_(out), n_(n), threaded_(threaded) {
+    if (threaded_) th_ = std::thread([this] { run(); });
+  }
+  void acquire() {                                   // before psim_snapshot_async on the next slot
+    if (!threaded_) return;
+    std::unique_lock<std::mutex> lk(m_);
+    cv_.wait(lk, [this] { return in_flight_ < PSIM_FRAME_SLOTS; });
+  }
+  void submit(int slot, int step) {
+    if (!threaded_) { write(slot, step); return; }
+    { std::lock_guard<std::mutex> lk(m_); q_.push_back({slot, step}); ++in_flight_; }
+    cv_.notify_all();
+  }
+  void finish() {
+    if (!threaded_) return;
+    { std::lock_guard<std::mutex> lk(m_); stop_ = true; }
+    cv_.notify_all();
+    if (th_.joinable()) th_.join();
+  }
+
+ private:
+  struct Job { int slot, step; };
+  void write(int slot, int step) {
+    const int32_t* id; const void *p, *v; const uint8_t* act;
+    gpu_check(psim_snapshot_wait(sim_, slot, &id, &p, &v, &act), "psim_snapshot_wait");
+    info("write for time step: " + std::to_string(step));
+    out_->write_frame(n_, id, p, v, act);
+  }
+  void run() {
+    for (;;) {
+      Job j;
+      {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [this] { return stop_ || !q_.empty(); });
+        if (q_.empty()) return;
+        j = q_.front(); q_.pop_front();
+      }
+      write(j.slot, j.step);
+      { std::lock_guard<std::mutex> lk(m_); --in_flight_; }
+      cv_.notify_all();
+    }
+  }
+  psim_sim* sim_; FrameWriter* out_; int64_t n_; bool threaded_;
+  std::thread th_; std::mutex m_; std::condition_variable cv_; std::deque<Job> q_;
+  int in_flight_ = 0; bool stop_ = false;
+};
+
 int main(int argc, char** argv) {
   std::vector<std::string> positional;
   int precision = 4;          // the reference computes in real32 (module_stoermer_verlet_method.f08:5)
   int device = -1;
   std::string algo = "cells";
+  bool sync_io = false;       // write frames from the stepping thread (no writer thread)
   bool io_selftest = false;   // parse both inputs, write the INITIAL state as one frame, no GPU (host-logic tests)
   for (int a = 1; a < argc; ++a) {
     std::string s = argv[a];
@@ -54,6 +118,7 @@ int main(int argc, char** argv) {
     else if (s == "--algo") algo = next();
     else if (s == "--quiet") g_quiet = true;
     else if (s == "--io-selftest") io_selftest = true;
+    else if (s == "--sync-io") sync_io = true;
     else positional.push_back(s);
   }
   info("get command arguments");
@@ -108,28 +173,27 @@ int main(int argc, char** argv) {
   info("start time integration");
   const auto t0 = std::chrono::steady_clock::now();
   const int wts = nl.write_time_step > 0 ? nl.write_time_step : nl.max_time_step + 1;
-  int pending_slot = -1, pending_step = 0, slot = 0;
-  auto drain = [&]() {
-    if (pending_slot < 0) return;
-    const int32_t* id; const void *p, *v; const uint8_t* act;
-    gpu_check(psim_snapshot_wait(sim, pending_slot, &id, &p, &v, &act), "psim_snapshot_wait");
-    info("write for time step: " + std::to_string(pending_step));
-    out->write_frame(n, id, p, v, act);
-    pending_slot = -1;
-  };
+  FramePipe pipe(sim, out, n, !sync_io);
+  int pending_slot = -1, pending_step = 0, slot = 0;   // --sync-io: write frame k-1 after enqueueing chunk k+1's snapshot
   int step = 0;
   while (step < nl.max_time_step) {
     const int chunk = std::min(wts - step % wts, nl.max_time_step - step);
     gpu_check(psim_advance(sim, chunk), "psim_advance");
     step += chunk;
     if (step % wts == 0) {
+      pipe.acquire();                                                     // the frame that used this slot is written
       gpu_check(psim_snapshot_async(sim, slot), "psim_snapshot_async");   // drains on a side stream
-      drain();                                                            // write the previous frame meanwhile
-      pending_slot = slot; pending_step = step;
+      if (sync_io) {
+        if (pending_slot >= 0) pipe.submit(pending_slot, pending_step);   // write the previous frame meanwhile
+        pending_slot = slot; pending_step = step;
+      } else {
+        pipe.submit(slot, step);
+      }
       slot = (slot + 1) % PSIM_FRAME_SLOTS;
     }
   }
-  drain();
+  if (sync_io && pending_slot >= 0) pipe.submit(pending_slot, pending_step);
+  pipe.finish();
   gpu_check(psim_synchronize(sim), "psim_synchronize");
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (!g_quiet) std::printf(" elapsed time in seconds: %.3f\n", secs);

@@ -275,9 +275,9 @@ allpairs_tcws_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
     const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(half * COLS);
     const unsigned dfull0 = pinned(smem_u32(&d_full[0])), dempty0 = pinned(smem_u32(&d_empty[0]));
     const int jbase = half * COLS;
-    // (Measured: a second register set to overlap the load of tile t + 1 with the reduction of tile t does
-    // not fit the 96-register budget of 640 threads; the spills cost 6x.  Overlap comes from the 4 warps per
-    // scheduler instead.)
+    // (Measured twice: a second register set to overlap the load of tile t + 1 with the reduction of tile t
+    // makes ptxas spill inside the loop at the 96-register cap of 672 threads: 7.6 ms against 6.8 ms.  Overlap
+    // comes from the 4 consumer warps per scheduler instead.)
 #ifdef PSIM_TC_PROF
     long long c_wait = 0, c_ld = 0, c_q = 0, p0 = clock64();
 #define PT(acc) { long long p1 = clock64(); acc += p1 - p0; p0 = p1; }

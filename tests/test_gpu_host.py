@@ -68,6 +68,27 @@ def test_simu_cli_end_to_end_against_oracle_frames(psim, oracle, tmp_path, preci
     assert size == precision * (4 + 2 * (1 + 7 * len(ids)))
 
 
+def test_simu_cli_writer_thread_file_is_byte_identical_to_sync_io(psim, tmp_path):
+    """Frame pipeline: with a frame every 2 steps (20 frames through 4 pinned slots) the
+    writer thread produces exactly the file the single-threaded path writes."""
+    from particle_simulation_b200 import build
+    nml = tmp_path / "fast.nml"
+    text = open(os.path.join(GOLDEN, "two_cubes.nml")).read()
+    import re
+    text = re.sub(r"(?i)(WRITE_TIME_STEP\s*=\s*)\d+", r"\g<1>2", text)
+    nml.write_text(text)
+    outs = []
+    for extra in ([], ["--sync-io"]):
+        out = str(tmp_path / ("run%d.output" % len(outs)))
+        r = subprocess.run([build.SIMU, str(nml), os.path.join(GOLDEN, "two_cubes.dat"), out, "--precision", "4", *extra],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        steps = [int(l.rsplit(":", 1)[1]) for l in r.stdout.splitlines() if "write for time step" in l]
+        assert steps == sorted(steps) and len(steps) == 20
+        outs.append(open(out, "rb").read())
+    assert outs[0] == outs[1] and len(outs[0]) > 4 * 4
+
+
 def test_frame_ring_matches_synchronous_frames(psim):
     ids, pos, vel = two_cubes()
     sim = psim.Simulation(psim.make_params(), ids, pos, vel, 4)
