@@ -280,6 +280,7 @@ def main():
     k0 = sim.counters()
     sim.advance(max(3, min(args.steps, 10)))
     k1 = sim.counters()
+    pin_now = sim.pairs_in_range()          # exact O(N^2) count at the positions of the last timed force launch
     sim.set_option(P.OPT_KERNEL_TIMING, 0)
     n_timed = k1.force_timed - k0.force_timed
     kernel_ms = (k1.force_ms - k0.force_ms) / max(1, n_timed)
@@ -328,7 +329,8 @@ def main():
             "survey_frac_of_fp32_fma_peak": survey_tflops / peak32 if peak32 else None,
             "survey_frac_of_fp64_fma_peak": survey_tflops / peak64 if peak64 else None,
             "pairs_in_range_per_step": int(sum_over_ranks(pin_own)),
-            "filter_pairs_per_step": int(sum_over_ranks(k1.filter_pairs)) if k1.filter_pairs >= 0 else None,
+            "filter_pairs_last_launch": int(sum_over_ranks(k1.filter_pairs)) if k1.filter_pairs >= 0 else None,
+            "pairs_in_range_last_launch": int(sum_over_ranks(pin_now)),    # equal: the filter dropped no pair
             "share_of_step": kernel_ms / (ms / args.steps) if ms > 0 else None,
             "hbm_bytes_per_launch_algorithmic": bytes_launch,
             "fp64_fma_peak": peak64, "fp32_fma_peak": peak32,

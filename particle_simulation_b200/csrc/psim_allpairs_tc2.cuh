@@ -28,8 +28,8 @@ namespace tc {
 constexpr int N2 = 128;                         // j records per tile of this kernel = accumulator columns per buffer
 constexpr int NBUF = 512 / N2;                  // TMEM ring: four accumulators of 128 columns
 constexpr int NCTL = NBUF;                      // MMA warps: warp w owns accumulator w, tiles t = w (mod NCTL)
-constexpr int NPAIR = 4;                        // shared-memory ring: 4 slots of two tiles (one 16 KB bulk copy each)
-constexpr int STAGES = 2 * NPAIR;               // 8 x 8 KB
+constexpr int NPAIR = 3;                        // shared-memory ring: 3 slots of two tiles (one 16 KB bulk copy each; 2: slower, 4: same)
+constexpr int STAGES = 2 * NPAIR;               // 6 x 8 KB
 constexpr int TILE_BYTES = N2 * K * 4;          // 8 KB
 constexpr int NQ = 4;                           // column groups: warp w reads TMEM lanes 32 (w % 4).., columns 32 (w / 4)..
 constexpr int CW = 4 * NQ;                      // consumer warps
