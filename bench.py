@@ -58,6 +58,8 @@ def parse_args():
     ap.add_argument("--no-cells", action="store_true", help="skip the cell-binned companion measurement")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--exact-diff", action="store_true", help="difference-form distance test (no pre-filter)")
+    ap.add_argument("--tc-pipelined", action="store_true", help="EXPERIMENTAL all-pairs kernel (option value 6, "
+                    "csrc/psim_allpairs_tc3.cuh): faster, but an intermittent launch failure is unresolved")
     ap.add_argument("--ffma2", action="store_true", help="all-pairs on the CUDA cores only (packed-FP32 filter kernel) "
                     "instead of the default tensor-core filter kernel")
     return ap.parse_args()
@@ -253,8 +255,8 @@ def main():
     sim = P.Simulation(params, ids, pos, vel, prec, device=local_rank, rank=rank, world=world, nccl_unique_id=uid)
     if args.algo == "cells":
         sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
-    if args.exact_diff or args.ffma2:
-        sim.set_option(P.OPT_EXACT_DIFF_FILTER, 1 if args.exact_diff else 5)
+    if args.exact_diff or args.ffma2 or args.tc_pipelined:
+        sim.set_option(P.OPT_EXACT_DIFF_FILTER, 1 if args.exact_diff else 5 if args.ffma2 else 6)
         sim.set_positions(pos.astype(native.rt(prec)))
     pairs_total = float(n) * (n - 1)
     n_own = sim.i_hi - sim.i_lo
@@ -320,7 +322,7 @@ def main():
         roofline = {
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak if peak else None, "traffic": traffic, "peak_source": peak_src,
-            "kernel": "allpairs_tcws_kernel", "kernel_ms": kernel_ms, "launches_timed": int(n_timed),
+            "kernel": "tcp::allpairs_tcws_kernel (experimental)" if args.tc_pipelined else "tc::allpairs_tcws_kernel", "kernel_ms": kernel_ms, "launches_timed": int(n_timed),
             "flops_per_launch": tensor_flops,
             "flops_accounting": "tensor pipe: 2*K = 32 flops per ordered pair tested (split-TF32 Gram matrix, K = 16); "
                                 "SURVEY.md 8(d)'s CUDA-core accounting (8 per pair tested + 15 per pair in range) is "

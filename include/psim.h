@@ -83,7 +83,10 @@ typedef enum psim_option {
                                     1: first-generation kernel with the distance test in difference form (3 sub,
                                       1 mul, 2 FMA, 1 compare per pair: the literal reading of stoermer:117-121);
                                     2: first-generation kernel with the pre-filter;
-                                    4: first, lock-step tensor-core kernel (kept for comparison).
+                                    4: first, lock-step tensor-core kernel (kept for comparison);
+                                    6: EXPERIMENTAL tensor-core kernel with software-pipelined consumers (measured
+                                      1.26x faster than 0, but one intermittent launch failure was seen and its fix
+                                      is unverified: csrc/psim_allpairs_tc3.cuh). Not for production use yet.
                                     All variants evaluate the same pairs with the same arithmetic; results differ
                                     by summation order only. */
 } psim_option;

@@ -23,6 +23,7 @@
 #include "psim_allpairs2.cuh"
 #include "psim_allpairs_tc.cuh"
 #include "psim_allpairs_tc2.cuh"
+#include "psim_allpairs_tc3.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -151,7 +152,7 @@ class SimT final : public psim_sim {
   static constexpr int RI = 2;                                    // i-particles per thread
   static constexpr int TS = 256;                                  // threads of the streaming kernels
   static constexpr int MAX_CLUSTER = 8;                           // portable cluster size limit
-  int variant = 0;      // 0 / 3: tensor-core filter kernel (default), 5: FFMA2 warp kernel, 1 / 2: v1 kernels, 4: lock-step tensor-core kernel
+  int variant = 0;      // 0 / 3: tensor-core filter kernel (default), 5: FFMA2 warp kernel, 1 / 2: v1 kernels, 4: lock-step tensor-core kernel, 6: experimental pipelined tensor-core kernel
   int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
   int warps_forced = 0;
@@ -406,6 +407,21 @@ class SimT final : public psim_sim {
       tc::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs);
       return PSIM_OK;
     }
+    if (variant == 6) {          // EXPERIMENTAL: pipelined consumers (psim_allpairs_tc3.cuh); opt-in until verified
+      *grid_out = blocks(i_hi - i_lo, tc::M);
+      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
+      if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
+      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, tc_pairs);
+      ++launches;
+      constexpr int kSmem = tcp::SMEM_BYTES;
+      static bool attr_set[64] = {false};
+      if (!attr_set[device & 63]) {
+        PSIM_CK(cudaFuncSetAttribute(tcp::allpairs_tcws_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_set[device & 63] = true;
+      }
+      tcp::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tcp::TW, kSmem, stream>>>(a, tc_bops, tc_pairs);
+      return PSIM_OK;
+    }
     if (variant == 4) {          // first, lock-step tensor-core version (kept for comparison)
       *grid_out = blocks(i_hi - i_lo, tc::M);
       constexpr int kPad = 120 * 1024;
@@ -624,7 +640,7 @@ class SimT final : public psim_sim {
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
     unsigned long long fp = 0;
-    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && (variant == 0 || variant == 3) && tc_pairs;
+    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && (variant == 0 || variant == 3 || variant == 6) && tc_pairs;
     if (tracked) PSIM_CK(cudaMemcpyAsync(&fp, tc_pairs, sizeof fp, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     out->filter_pairs = tracked ? (int64_t)fp : -1;
@@ -646,7 +662,7 @@ class SimT final : public psim_sim {
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
       case PSIM_OPT_EXACT_DIFF_FILTER:
-        if (value < 0 || value > 5) return PSIM_ERR_INVALID_ARGUMENT;
+        if (value < 0 || value > 6) return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
     }

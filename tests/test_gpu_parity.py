@@ -9,6 +9,8 @@ summation order only:
 Trajectories are chaotic; K-step comparisons use short horizons and
   f64: 1e-9 absolute on positions,  f32: 2e-4.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -35,8 +37,13 @@ def _select(psim, sim, algo):
         sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)
 
 
+# the experimental pipelined tensor-core kernel (value 6) is only exercised on request: one intermittent launch
+# failure was seen with it (csrc/psim_allpairs_tc3.cuh), and a failed launch poisons the CUDA context of the session
+EXPERIMENTAL = ["allpairs_tensor_pipelined"] if os.environ.get("PSIM_TEST_EXPERIMENTAL") == "1" else []
+
+
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "allpairs_tensor", "allpairs_tensor_lockstep", "allpairs_ffma2", "cells"])
+@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "allpairs_tensor", "allpairs_tensor_lockstep", "allpairs_ffma2", "cells"] + EXPERIMENTAL)
 def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     ids, pos, vel = two_cubes()
     p = psim.make_params()
@@ -58,6 +65,9 @@ def test_initial_forces_match_oracle(psim, oracle, precision, variant):
         sim.set_positions(pos)
     elif variant == "allpairs_ffma2":
         sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)
+        sim.set_positions(pos)
+    elif variant == "allpairs_tensor_pipelined":
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 6)
         sim.set_positions(pos)
     elif variant.startswith("cells"):
         _select(psim, sim, variant)
@@ -160,8 +170,9 @@ def test_conservation_and_energy(psim, oracle, algo):
 
 
 @pytest.mark.parametrize("precision", [4, 8])
+@pytest.mark.parametrize("kernel", [0] + ([6] if EXPERIMENTAL else []))
 @pytest.mark.parametrize("case", ["lattice_65536", "hot_gas_32768", "two_cubes"])
-def test_tensor_core_filter_drops_no_pair(psim, precision, case):
+def test_tensor_core_filter_drops_no_pair(psim, precision, case, kernel):
     """The tensor-core distance filter (split-TF32 Gram matrix) must be conservative: the ordered in-range
     pairs its exact path evaluated (psim_counters.filter_pairs) equal the exact O(N^2) count, and stay equal
     while the configuration moves.  The forces then agree with the default kernel's up to summation order
@@ -183,6 +194,9 @@ def test_tensor_core_filter_drops_no_pair(psim, precision, case):
     ref.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)        # the CUDA-core kernel
     ref.set_positions(pos)
     sim = psim.Simulation(params, ids, pos, vel, precision)   # default: the tensor-core kernel
+    if kernel:
+        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, kernel)
+        sim.set_positions(pos)
     for round_ in range(3):
         exact = sim.pairs_in_range()
         assert exact > 0
