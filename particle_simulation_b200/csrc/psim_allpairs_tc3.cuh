@@ -9,8 +9,8 @@
 //     * psim_allpairs_tc2.cuh never failed in the same runs (full suites, 1/2/4/8-GPU benches);
 //     * a visible difference in SASS: tc2 has BSYNC + WARPSYNC.ALL between every mbarrier.try_wait spin loop
 //       and the .sync.aligned tcgen05.ld; here ptxas keeps the loop state in uniform registers, treats the
-//       try_wait result as warp-uniform and emits neither — an explicit __syncwarp() after the wait (below) is
-//       compiled to NOPs.  If lanes CAN leave the spin an iteration apart, the .aligned load runs with a
+//       try_wait result as warp-uniform and emits neither — an explicit __syncwarp() after the wait is
+//       compiled to NOPs; the wait now loops on __all_sync (mbar_wait_warp), unverified.  If lanes CAN leave the spin an iteration apart, the .aligned load runs with a
 //       partial warp; if the hardware guarantees a uniform result, this is not the cause.
 //     * next steps: identify the failing launch with error checks after every launch in a loop of a few
 //       hundred force calls; bisect dense entries / segment re-entry / the REDUX'ed start tile / the 3-slot
@@ -54,6 +54,16 @@ constexpr unsigned DENSE = 0x8000u;             // queue entry: [dense:1][tile -
 
 // tc_prepare_kernel (same 128-record B tiles), mbar_init / mbar_arrive / mbar_expect_tx / bulk_copy_g2s /
 // umma_commit: psim_allpairs_tc2.cuh.
+
+// Wait for an mbarrier phase with the whole warp and leave the spin loop in the SAME iteration in all lanes
+// (the vote is a real warp-synchronous instruction; a bare __syncwarp() after mbar_wait is elided by ptxas here).
+__device__ __forceinline__ void mbar_wait_warp(unsigned addr, unsigned parity) {
+  unsigned done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                 : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!__all_sync(0xffffffffu, done));
+}
 
 // The exact path: every queued candidate j of row ig in the working precision, with the reference's own
 // arithmetic (pair_force, psim_common.cuh).  A dense entry expands to its 32 columns.
@@ -169,8 +179,7 @@ __device__ __noinline__ unsigned long long consume_tiles(float cut, unsigned q, 
   const int t_begin = (int)__reduce_max_sync(0xffffffffu, (unsigned)t_begin_v);
 #define PSIM_TC_ACQUIRE(r, buf, par_)                                                            \
   {                                                                                              \
-    mbar_wait(dbar0 + 8u * (buf), (par_));                                                       \
-    __syncwarp();   /* lanes may leave the spin an iteration apart; the .aligned load needs them all */ \
+    mbar_wait_warp(dbar0 + 8u * (buf), (par_));   /* all lanes leave together: .aligned load next */ \
     asm volatile("tcgen05.fence::after_thread_sync;");                                           \
     PSIM_TMEM_LD32(r, lane_base + (unsigned)((buf) * N2));                                       \
   }
