@@ -175,3 +175,42 @@ def test_single_particle_and_isolated_pair(oracle):
     f = o.aux()[2]
     assert f[0, 0] == pytest.approx(24.0155998, rel=1e-8) and f[1, 0] == -f[0, 0]
     assert np.all(f[:, 1:] == 0)
+
+
+def _shipped():
+    """BASELINE.json configs[0]: the reference's own test_particles.dat + environment_params.nml, carried inside
+    the fixture (tests/golden/make_golden_shipped.py; /root/reference does not exist on the GPU box)."""
+    return np.load(os.path.join(GOLDEN, "shipped_test_particles_golden.npz"))
+
+
+def _shipped_params(mod, g, nb_of_threads=None):
+    return mod.make_params(delta_t=float(g["delta_t"]), epsilon=float(g["epsilon"]), sigma=float(g["sigma"]),
+                           mass=float(g["mass"]), r_cut=float(g["r_cut"]), length_of_area=tuple(g["length_of_area"]),
+                           length_of_cell=tuple(g["length_of_cell"]),
+                           nb_of_threads=int(g["nb_of_threads"]) if nb_of_threads is None else nb_of_threads)
+
+
+# f32 tolerances: coordinates up to ~50 carry ~4e-6 of rounding, the force slope at the lattice spacing is ~57
+@pytest.mark.parametrize("threads", [3, 1])            # the shipped namelist runs 3 OpenMP threads
+@pytest.mark.parametrize("precision,ftol,xtol", [(8, 1e-12, 1e-9), (4, 5e-4, 5e-4)])
+def test_oracle_on_the_shipped_case_matches_numpy_golden(oracle, precision, ftol, xtol, threads):
+    g = _shipped()
+    o = oracle.Oracle(_shipped_params(oracle, g, threads), precision, g["ids"], g["x0"], g["v0"])
+    assert o.n_active == len(g["ids"]) == 2000
+    f0 = o.aux()[2]
+    assert np.abs(f0 - g["f0"]).max() <= ftol * np.abs(g["f0"]).max()
+    fb, pairs = oracle.bruteforce(_shipped_params(oracle, g, threads), precision, g["x0"])
+    assert pairs in (int(g["pairs0"]), int(g["pairs0"]) // 2)          # ordered pairs in the golden
+    assert np.abs(fb - g["f0"]).max() <= ftol * np.abs(g["f0"]).max()
+    o.advance(int(g["k_steps"]))                       # one frame interval: the reference's first frame
+    _, x, v, a = o.frame()
+    assert a.all()
+    assert np.abs(x - g["x"]).max() <= xtol
+    assert np.abs(v - g["v"]).max() <= 100 * xtol
+    fn = o.aux()[2]
+    assert np.abs(fn - g["f"]).max() <= (1e-9 if precision == 8 else 2e-2) * np.abs(g["f"]).max()
+    assert o.rebuilds >= 1                             # 0.005 per step against dr_max_tolerable = 0.5: lists were rebuilt
+    k, u, mom = o.energy()
+    assert k == pytest.approx(g["e1"][0], rel=1e-4 if precision == 4 else 1e-10)
+    assert np.abs(mom - g["e1"][2:]).max() <= (1e-2 if precision == 4 else 1e-8)
+    o.close()
