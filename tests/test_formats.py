@@ -132,6 +132,39 @@ def test_cpp_host_io_agrees_with_python(tmp_path, precision):
     assert open(out_cpp, "rb").read() == open(out_py, "rb").read()
 
 
+REFERENCE = "/root/reference"
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REFERENCE, "particle_files")),
+                    reason="the reference checkout only exists in the build container")
+@pytest.mark.parametrize("name,count", [("test_particles.dat", 2000), ("more_test_particles.dat", 39440)])
+def test_both_hosts_read_the_reference_s_own_files(tmp_path, name, count):
+    """BASELINE.json configs[0..1]: the shipped environment_params.nml and particle files go through the C++
+    readers (simu_b200 --io-selftest) and the Python readers to the same .output bytes, in the reference's
+    4-byte-record layout (program_...:54-56, 327-365).  particle_files/big_body_test.dat is not in the checkout
+    (.MISSING_LARGE_BLOBS).  Nothing is copied: the files are read where they lie."""
+    from particle_simulation_b200 import build, formats
+    simu = build.build_host() or build.SIMU
+    nml, dat = os.path.join(REFERENCE, "environment_params.nml"), os.path.join(REFERENCE, "particle_files", name)
+    n = formats.read_namelist(nml)
+    assert (n["nb_of_threads"], n["write_time_step"], n["max_time_step"]) == (3, 100, 5001)
+    assert n["length_of_area"] == [99.0, 99.0, 99.0] and n["length_of_cell"] == [3.0, 3.0, 3.0]
+    assert (n["sigma"], n["epsilon"], n["mass"], n["r_cut"], n["delta_t"]) == (1.0, 1.0, 1.0, 2.5, 0.001)
+    ids, pos, vel = formats.read_particles(dat)
+    assert len(ids) == count and pos.shape == vel.shape == (count, 3)
+    out_cpp, out_py = str(tmp_path / "cpp.output"), str(tmp_path / "py.output")
+    r = subprocess.run([simu, nml, dat, out_cpp, "--io-selftest", "--precision", "4"], capture_output=True, text=True, check=True)
+    assert "Number of particles in file: %d" % count in r.stdout
+    with formats.OutputWriter(out_py, n["length_of_area"], nbytes=4) as w:
+        w.write_frame(ids, pos, vel)
+    data = open(out_cpp, "rb").read()
+    assert data == open(out_py, "rb").read()
+    assert len(data) == 4 * (4 + 1 + 7 * count)                     # area[3], frame count, then 7 n + 1 records
+    area, declared, frames = formats.read_output(out_cpp, nbytes=4)
+    assert area == [99.0, 99.0, 99.0] and declared == 1 and np.array_equal(frames[0][0], ids)
+    assert np.array_equal(frames[0][1], pos.astype(np.float32)) and np.array_equal(frames[0][2], vel.astype(np.float32))
+
+
 def test_cpp_host_reference_error_behaviour(tmp_path):
     """Wrong argument count / missing file / empty particle file: message on stderr and
     exit status 0, as stop_program's bare `stop` does (aux:24-49)."""
