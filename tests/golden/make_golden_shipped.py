@@ -12,7 +12,13 @@ frame (program_particle_simulation_openmp.f08:109-115).  Every particle stays in
 horizon (0.5 length units of travel), so the reference's rebuilds (displacement resets) have no physical effect
 and brute force is its exact physical equivalent.
 
-Writes tests/golden/shipped_test_particles_golden.npz (binary; no reference text is copied into the repo).
+A second fixture covers particle_files/more_test_particles.dat (N = 39,440: a 16^3 body at speed 10 towards a
+35,344-particle slab), forces at t = 0 only.  A dense pair matrix would need 12 GB, so the pairs come from a
+KD-tree (scipy.spatial.cKDTree.query_pairs, r <= r_cut) and the strict r < r_cut test and the force formula are
+then applied in numpy float64, accumulated with np.add.at — again sharing no code with the oracle or CUDA path.
+
+Writes tests/golden/shipped_test_particles_golden.npz and shipped_more_test_particles_golden.npz
+(binary; no reference text is copied into the repo).
 """
 import os
 import sys
@@ -59,5 +65,53 @@ def main():
     print("energy drift", (e1[0] + e1[1]) - (e0[0] + e0[1]), "of", e0[0] + e0[1])
 
 
+def forces_kdtree(x, p, mg):
+    from scipy.spatial import cKDTree
+    r_min, r_cut, F_rcut, _ = mg.constants(p)
+    pairs = cKDTree(x).query_pairs(r_cut * (1.0 + 1e-12), output_type="ndarray")     # i < j, a hair generous
+    d = x[pairs[:, 0]] - x[pairs[:, 1]]                                            # r_ij = x_i - x_j
+    r = np.sqrt((d * d).sum(-1))
+    keep = r < r_cut                                                               # stoermer:121, strict
+    pairs, d, r = pairs[keep], d[keep], r[keep]
+    s = (r_min / r) ** 6
+    fij = -(d * (12.0 * p["epsilon"] * ((s / (r * r)) * (1.0 - s) - F_rcut))[:, None])   # force on i
+    f = np.zeros_like(x)
+    np.add.at(f, pairs[:, 0], fij)
+    np.add.at(f, pairs[:, 1], -fij)
+    return f, 2 * len(pairs)
+
+
+def main_more():
+    import make_golden as mg
+    from particle_simulation_b200 import formats
+
+    nml = formats.read_namelist(os.path.join(REF, "environment_params.nml"))
+    ids, x, v = formats.read_particles(os.path.join(REF, "particle_files", "more_test_particles.dat"))
+    p = dict(sigma=nml["sigma"], epsilon=nml["epsilon"], mass=nml["mass"], r_cut=nml["r_cut"], delta_t=nml["delta_t"],
+             length_of_area=tuple(nml["length_of_area"]), length_of_cell=tuple(nml["length_of_cell"]))
+    area = np.array(p["length_of_area"])
+    assert (x > 0).all() and (x < area).all()
+    f0, pairs0 = forces_kdtree(x, p, mg)
+    # cross-check the KD-tree route against the dense route of make_golden.py on the first body
+    sub = slice(0, 4096)
+    near = np.zeros(len(x), bool); near[sub] = True
+    fd, _ = mg.forces(x[sub], p)
+    from scipy.spatial import cKDTree
+    touching = cKDTree(x[~near]).query_ball_point(x[sub], p["r_cut"] * p["sigma"] * 1.001, return_length=True)
+    iso = touching == 0                                                            # rows of body 1 with no neighbour in body 2
+    assert iso.any() and np.abs(fd[iso] - f0[sub][iso]).max() <= 1e-12 * np.abs(fd).max()
+    np.savez_compressed(
+        os.path.join(HERE, "shipped_more_test_particles_golden.npz"),
+        ids=ids, x0=x.astype(np.float32), v0=v.astype(np.float32), f0=f0, pairs0=pairs0,
+        nb_of_threads=int(nml["nb_of_threads"]), sigma=p["sigma"], epsilon=p["epsilon"], mass=p["mass"], r_cut=p["r_cut"],
+        delta_t=p["delta_t"], length_of_area=area, length_of_cell=np.array(p["length_of_cell"]))
+    # x0/v0 are stored as float32 to keep the fixture small: the file's 4-decimal values below 100 survive the round
+    # trip through float32 exactly AFTER re-rounding to 4 decimals, which the loader does
+    back = np.round(x.astype(np.float32).astype(np.float64), 4)
+    assert np.array_equal(back, x) and np.array_equal(np.round(v.astype(np.float32).astype(np.float64), 4), v)
+    print("golden written: N=%d, ordered pairs in range at t=0 %d, max |f| %.6g" % (len(ids), pairs0, np.abs(f0).max()))
+
+
 if __name__ == "__main__":
     main()
+    main_more()

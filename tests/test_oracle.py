@@ -214,3 +214,29 @@ def test_oracle_on_the_shipped_case_matches_numpy_golden(oracle, precision, ftol
     assert k == pytest.approx(g["e1"][0], rel=1e-4 if precision == 4 else 1e-10)
     assert np.abs(mom - g["e1"][2:]).max() <= (1e-2 if precision == 4 else 1e-8)
     o.close()
+
+
+def _shipped_more():
+    """particle_files/more_test_particles.dat (N = 39,440) inside its fixture; positions and velocities are stored
+    as float32 and re-rounded to the file's 4 decimals (exact, checked by the generator)."""
+    g = np.load(os.path.join(GOLDEN, "shipped_more_test_particles_golden.npz"))
+    x0 = np.round(g["x0"].astype(np.float64), 4)
+    v0 = np.round(g["v0"].astype(np.float64), 4)
+    return g, x0, v0
+
+
+@pytest.mark.parametrize("precision,ftol", [(8, 1e-12), (4, 5e-4)])
+def test_oracle_on_the_larger_shipped_case_matches_kdtree_golden(oracle, precision, ftol):
+    """Forces at t = 0 on the reference's own N = 39,440 input: the oracle's cell lists (3 slices, as shipped) and its
+    internal brute force against a KD-tree + numpy evaluation (tests/golden/make_golden_shipped.py)."""
+    g, x0, v0 = _shipped_more()
+    p = _shipped_params(oracle, g)
+    o = oracle.Oracle(p, precision, g["ids"], x0, v0)
+    assert o.n_active == 39440
+    scale = np.abs(g["f0"]).max()
+    assert np.abs(o.aux()[2] - g["f0"]).max() <= ftol * scale
+    fb, pairs = oracle.bruteforce(p, precision, x0)
+    assert np.abs(fb - g["f0"]).max() <= ftol * scale
+    if precision == 8:
+        assert pairs in (int(g["pairs0"]), int(g["pairs0"]) // 2)
+    o.close()
