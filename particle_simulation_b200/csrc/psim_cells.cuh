@@ -64,7 +64,8 @@ template <class R, int MODE, int QCAP, int T>
 __global__ void __launch_bounds__(T)
 cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const int32_t* __restrict__ cell_of,
                   const int32_t* __restrict__ cell_start, const int32_t* __restrict__ own_slots,
-                  const int32_t* __restrict__ own_start, const int32_t* __restrict__ perm, int ncell) {
+                  const int32_t* __restrict__ own_start, const int32_t* __restrict__ perm, int ncell,
+                  unsigned long long* __restrict__ tested) {
   constexpr int W = T / 32, TJ = 32;
   __shared__ int32_t queue[QCAP * T];
   __shared__ __align__(16) float tx[W][2][TJ], ty[W][2][TJ], tz[W][2][TJ], tw[W][2][TJ];
@@ -100,6 +101,8 @@ cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const 
   }
 
   int cnt = 0;
+  unsigned ntest = 0;          // distance tests of this warp (active lanes x valid records), reported when asked for
+  const unsigned nactive = __popc(__ballot_sync(0xffffffffu, cell < ncell));
   // Two queue entries per trip: independent chains (sqrt, two divisions each) that the
   // scheduler interleaves; the additions keep queue order, so the sum stays deterministic.
   auto flush = [&]() {
@@ -152,6 +155,7 @@ cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const 
           // room for a whole tile in every lane's queue, decided for the warp as one
           if (__any_sync(0xffffffffu, cnt > QCAP - TJ)) { flush(); qidx = tid; }
           const bool more = t0 + TJ < tb;
+          ntest += nactive * (unsigned)min(TJ, tb - t0);
           Real4<R> pre;
           if (more) pre = fetch(t0 + TJ + lane, tb);   // in flight during this tile's filter
           const float2 px = make_float2(fxi, fxi), py = make_float2(fyi, fyi), pz = make_float2(fzi, fzi);
@@ -186,6 +190,7 @@ cell_force_kernel(const StepArgs<R> a, const Real4<R>* __restrict__ posj, const 
       }
     }
     flush();
+    if (tested && lane == 0) atomicAdd(tested, (unsigned long long)ntest);
   }
 
   R first = (R)0, second = (R)0;
@@ -201,9 +206,8 @@ struct HouseArgs {
   Real4<R>* pos_new;      // the buffer the drift just filled (the current one from here on)
   Real4<R>* pos_other;    // the other buffer: next step's target
   Real4<R>* disp;
-  const R* rank_pairs;    // [2 * world] every rank's two largest |disp| (null: no trigger this call)
+  const R* rank_pairs;    // [world][slices][2] every rank's two largest |disp| per trigger slice (null: no trigger this call)
   int world;
-  int flag_in_ctrl;       // NB_OF_THREADS > 1: slice_trigger_kernel already wrote ctrl->flag[parity]
   Control* ctrl;
   int parity;
   int64_t n, i_lo, i_hi;
@@ -242,8 +246,8 @@ __device__ __forceinline__ void block_scan_256(const unsigned* cnt, int32_t* sta
 }
 
 // One cooperative launch per step (256 threads per block, grid = what is co-resident).
-//  1. trigger: dr_max_first + dr_max_second > dr_max_tolerable over the merged per-rank pairs
-//     (stoermer:168-185); every block computes it for itself from <= 8 pairs.
+//  1. trigger: dr_max_first + dr_max_second > dr_max_tolerable (stoermer:168-185) per NB_OF_THREADS slice
+//     (program:71,86,92) over the merged per-rank pairs; every block computes it for itself.
 //  2. if it fired: the observable side effects of update_neighbor_list_and_cell_space
 //     (pm:112-124): displacement reset (pm:158), deactivation of particles whose cell index left
 //     the grid (pm:440-441, 503-504, 534-552);
@@ -261,16 +265,23 @@ housekeeping_kernel(const HouseArgs<R> h) {
   const int64_t gtid = (int64_t)blockIdx.x * 256 + threadIdx.x;
   const int64_t gsz = (int64_t)gridDim.x * 256;
 
-  int flag = 0;
-  if (h.flag_in_ctrl) {
-    flag = h.ctrl->flag[h.parity];
-  } else if (h.rank_pairs) {
-    R first = (R)0, second = (R)0;
-    for (int r = 0; r < 2 * h.world; ++r) top2_push(first, second, h.rank_pairs[r]);
-    flag = r_add(first, second) > c.dr_max_tolerable ? 1 : 0;
+  // The reference's trigger, slice by slice (program:71,86,92): the two largest |disp| of a slice are the
+  // two largest among the ranks' pairs for that slice; any slice over the tolerance fires the rebuild.
+  int mine = 0;
+  if (h.rank_pairs) {
+    for (int k = threadIdx.x; k < c.slices; k += 256) {
+      R first = (R)0, second = (R)0;
+      for (int r = 0; r < h.world; ++r) {
+        const R* pr = h.rank_pairs + 2 * ((size_t)r * c.slices + k);
+        top2_push(first, second, pr[0]);
+        top2_push(first, second, pr[1]);
+      }
+      if (r_add(first, second) > c.dr_max_tolerable) mine = 1;
+    }
   }
+  const int flag = __syncthreads_or(mine);
   if (gtid == 0) {
-    if (!h.flag_in_ctrl) h.ctrl->flag[h.parity] = flag;
+    h.ctrl->flag[h.parity] = flag;
     if (flag) h.ctrl->rebuilds += 1;
   }
   if (gtid == 1 || (gtid == 0 && gsz == 1)) h.ctrl->flag[h.parity ^ 1] = 0;
@@ -362,13 +373,14 @@ struct CellPath {
   int32_t *cell_of = nullptr, *own_slots = nullptr;
   unsigned *count = nullptr, *own_count = nullptr, *fill = nullptr;
   Real4<R>* posj = nullptr;
+  unsigned long long* tested = nullptr;  // distance tests of the last counted force launch (PSIM_OPT_KERNEL_TIMING)
 
   bool allocated() const { return key != nullptr; }
-  const int32_t* orig_or_null() const { return nullptr; }   // the state is always in array order
 
   void destroy() {
     cudaFree(key); cudaFree(perm); cudaFree(cell_start); cudaFree(own_start); cudaFree(cell_of);
-    cudaFree(own_slots); cudaFree(count); cudaFree(own_count); cudaFree(fill); cudaFree(posj);
+    cudaFree(own_slots); cudaFree(count); cudaFree(own_count); cudaFree(fill); cudaFree(posj); cudaFree(tested);
+    tested = nullptr;
     key = perm = cell_start = own_start = cell_of = own_slots = nullptr;
     count = own_count = fill = nullptr; posj = nullptr;
     binned = false;
@@ -394,6 +406,8 @@ struct CellPath {
     PSIM_TRY(cudaMalloc(&cell_of, sizeof(int32_t) * n_pad));
     PSIM_TRY(cudaMalloc(&own_slots, sizeof(int32_t) * n_pad));
     PSIM_TRY(cudaMalloc(&posj, sizeof(Real4<R>) * n_pad));
+    PSIM_TRY(cudaMalloc(&tested, sizeof *tested));
+    PSIM_TRY(cudaMemsetAsync(tested, 0, sizeof *tested, sim.stream));
     PSIM_TRY(cudaMemsetAsync(count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
     PSIM_TRY(cudaMemsetAsync(own_count, 0, sizeof(unsigned) * (ncell + 1), sim.stream));
     PSIM_TRY(cudaMemsetAsync(own_start, 0, sizeof(int32_t) * (ncell + 2), sim.stream));
@@ -419,15 +433,17 @@ struct CellPath {
     const int64_t n_own = sim.i_hi - sim.i_lo;
     if (n_own <= 0) return PSIM_OK;
     const unsigned grid = (unsigned)((n_own + TF - 1) / TF);
+    unsigned long long* cnt = sim.timing ? tested : nullptr;      // counting costs a memset per launch: only on request
+    if (cnt && cudaMemsetAsync(cnt, 0, sizeof *cnt, sim.stream) != cudaSuccess) return PSIM_ERR_CUDA;
     if (mode == MODE_FORCE)
       cell_force_kernel<R, MODE_FORCE, QCAP, TF><<<grid, TF, 0, sim.stream>>>(
-          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell);
+          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell, cnt);
     else if (mode == MODE_FORCE_KICK)
       cell_force_kernel<R, MODE_FORCE_KICK, QCAP, TF><<<grid, TF, 0, sim.stream>>>(
-          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell);
+          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell, cnt);
     else
       cell_force_kernel<R, MODE_FORCE_KICK_DRIFT, QCAP, TF><<<grid, TF, 0, sim.stream>>>(
-          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell);
+          a, posj, cell_of, cell_start, own_slots, own_start, perm, ncell, cnt);
     ++launches;
     return PSIM_OK;
   }

@@ -63,28 +63,24 @@ kick_kernel(const Real4<R>* __restrict__ pos, Real4<R>* __restrict__ vel, const 
 
 // NB_OF_THREADS > 1: the reference evaluates the trigger per thread slice
 // (program_particle_simulation_openmp.f08:71,86,92; slices :305-323).  One
-// block per slice scans |disp| (disp.w) of its slice and ORs its verdict in.
-// ctrl->flag[parity] must be 0 on entry (the housekeeping kernel of the previous
-// step clears it).
+// block per slice scans |disp| (disp.w) of the part of its slice that this
+// handle owns ([i_lo, i_hi): everything on a single GPU, the shard on a
+// sharded handle) and writes the two largest values to out[2 * slice .. + 1]
+// (zeros when the intersection is empty).  The housekeeping kernel merges the
+// ranks' pairs slice by slice and ORs the verdicts.
 template <class R>
 __global__ void __launch_bounds__(256)
-slice_trigger_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restrict__ disp,
-                     const int32_t* __restrict__ orig, int64_t n, Control* ctrl, int parity, Consts<R> c) {
+slice_top2_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restrict__ disp, int64_t n,
+                  int64_t i_lo, int64_t i_hi, R* __restrict__ out, Consts<R> c) {
   __shared__ R s_first[8], s_second[8];
   const int64_t per = n / c.slices;
-  const int64_t lo = per * blockIdx.x;
-  const int64_t hi = (blockIdx.x == (unsigned)c.slices - 1) ? n : per * (blockIdx.x + 1);
+  int64_t lo = per * blockIdx.x;
+  int64_t hi = (blockIdx.x == (unsigned)c.slices - 1) ? n : per * (blockIdx.x + 1);
+  if (lo < i_lo) lo = i_lo;
+  if (hi > i_hi) hi = i_hi;
   R first = (R)0, second = (R)0;
-  if (orig) {
-    // state is cell-ordered: visit every slot, keep those whose particle index is in the slice
-    for (int64_t k = threadIdx.x; k < n; k += 256) {
-      const int64_t i = orig[k];
-      if (i >= lo && i < hi && !(pos[k].w >= c.huge)) top2_push(first, second, disp[k].w);
-    }
-  } else {
-    for (int64_t i = lo + threadIdx.x; i < hi; i += 256)
-      if (!(pos[i].w >= c.huge)) top2_push(first, second, disp[i].w);
-  }
+  for (int64_t i = lo + threadIdx.x; i < hi; i += 256)
+    if (!(pos[i].w >= c.huge)) top2_push(first, second, disp[i].w);
   top2_warp_reduce(first, second);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) { s_first[warp] = first; s_second[warp] = second; }
@@ -93,7 +89,7 @@ slice_trigger_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restric
     first = lane < 8 ? s_first[lane] : (R)0;
     second = lane < 8 ? s_second[lane] : (R)0;
     top2_warp_reduce(first, second);
-    if (lane == 0 && r_add(first, second) > c.dr_max_tolerable) atomicOr(&ctrl->flag[parity], 1);
+    if (lane == 0) { out[2 * blockIdx.x] = first; out[2 * blockIdx.x + 1] = second; }
   }
 }
 
@@ -103,17 +99,15 @@ slice_trigger_kernel(const Real4<R>* __restrict__ pos, const Real4<R>* __restric
 template <class R, int T>
 __global__ void __launch_bounds__(T)
 init_positions_kernel(Real4<R>* __restrict__ pos_a, Real4<R>* __restrict__ pos_b, const R* __restrict__ xyz,
-                      const unsigned char* __restrict__ active_in, const int32_t* __restrict__ orig,
-                      int64_t n, int64_t n_pad, Consts<R> c) {
+                      const unsigned char* __restrict__ active_in, int64_t n, int64_t n_pad, Consts<R> c) {
   const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
   if (i >= n_pad) return;
   Real4<R> p; p.x = p.y = p.z = (R)0; p.w = c.huge;
   if (i < n) {
-    const int64_t o = orig ? orig[i] : i;      // slot i holds particle o
-    p.x = xyz[3 * o]; p.y = xyz[3 * o + 1]; p.z = xyz[3 * o + 2];
+    p.x = xyz[3 * i]; p.y = xyz[3 * i + 1]; p.z = xyz[3 * i + 2];
     bool ok = !(p.x > c.area[0] || p.y > c.area[1] || p.z > c.area[2] || p.x < (R)0 || p.y < (R)0 || p.z < (R)0);
     ok = ok && inside_grid(p.x, p.y, p.z, c);
-    if (active_in) ok = active_in[o] != 0;     // operator form: the caller decides
+    if (active_in) ok = active_in[i] != 0;     // operator form: the caller decides
     p.w = ok ? filter_weight(p.x, p.y, p.z, c) : c.huge;
   }
   pos_a[i] = p;
@@ -133,24 +127,22 @@ unpack3_kernel(Real4<R>* __restrict__ dst, const R* __restrict__ xyz, int64_t n,
 // Pack a record array into xyz triples (frame output / diagnostics).
 template <class R, int T>
 __global__ void __launch_bounds__(T)
-pack3_kernel(R* __restrict__ xyz, const Real4<R>* __restrict__ src, const int32_t* __restrict__ orig,
-             int64_t lo, int64_t hi) {
+pack3_kernel(R* __restrict__ xyz, const Real4<R>* __restrict__ src, int64_t lo, int64_t hi) {
   const int64_t i = lo + (int64_t)blockIdx.x * T + threadIdx.x;
   if (i >= hi) return;
   const Real4<R> v = src[i];
-  const int64_t o = orig ? orig[i] : i;        // back to array order
-  xyz[3 * o] = v.x; xyz[3 * o + 1] = v.y; xyz[3 * o + 2] = v.z;
+  xyz[3 * i] = v.x; xyz[3 * i + 1] = v.y; xyz[3 * i + 2] = v.z;
 }
 
 template <class R, int T>
 __global__ void __launch_bounds__(T)
-pack_active_kernel(unsigned char* __restrict__ active, const Real4<R>* __restrict__ pos,
-                   const int32_t* __restrict__ orig, int64_t n, Consts<R> c, Control* ctrl) {
+pack_active_kernel(unsigned char* __restrict__ active, const Real4<R>* __restrict__ pos, int64_t n, Consts<R> c,
+                   Control* ctrl) {
   const int64_t i = (int64_t)blockIdx.x * T + threadIdx.x;
   bool act = false;
   if (i < n) {
     act = !(pos[i].w >= c.huge);
-    if (active) active[orig ? orig[i] : i] = act ? 1 : 0;
+    if (active) active[i] = act ? 1 : 0;
   }
   const unsigned m = __ballot_sync(0xffffffffu, act);
   if ((threadIdx.x & 31) == 0 && m) atomicAdd(&ctrl->n_active, (unsigned long long)__popc(m));
