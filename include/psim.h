@@ -57,7 +57,8 @@ typedef struct psim_params {
   int32_t nb_of_threads;     /* NB_OF_THREADS: the reference evaluates its
                                 rebuild trigger per thread slice
                                 (program_...:71,86,92; slices :305-323); the
-                                device reproduces that per-slice trigger.  <=0 means 1. */
+                                device reproduces that per-slice trigger, on
+                                single-GPU and on sharded handles.  <=0 means 1. */
   int32_t reserved;
 } psim_params;
 
@@ -69,26 +70,26 @@ typedef enum psim_force_algo {
                                 single-GPU and sharded handles */
 } psim_force_algo;
 
+/* Which kernel runs the all-pairs force pass.  All of them evaluate the same pairs with the same arithmetic
+ * (one rounding per operation in the order of stoermer:117-128); results differ by summation order only. */
+typedef enum psim_allpairs_kernel {
+  PSIM_ALLPAIRS_TENSOR = 0,          /* default: the distance filter of every ordered pair runs on the tensor cores
+                                        (tcgen05.mma kind::tf32 on split operands, TMEM accumulators, TMA-fed), the
+                                        exact pair arithmetic on the CUDA cores for the few pairs that pass.  The
+                                        round-1 values 3 and 6 are accepted as aliases. */
+  PSIM_ALLPAIRS_DIFFERENCE_FORM = 1, /* the distance test in difference form in the working precision (3 sub, 1 mul,
+                                        2 FMA, 1 compare per pair: the literal reading of stoermer:117-121), no
+                                        pre-filter; ~5x slower, kept as the plainest statement of the path */
+  PSIM_ALLPAIRS_CUDA_CORE = 5        /* warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in packed
+                                        FP32 (3 FMAs per ordered pair); no tensor cores; 1.5-2x slower than 0 */
+} psim_allpairs_kernel;
+
 typedef enum psim_option {
   PSIM_OPT_FORCE_ALGO = 0,      /* psim_force_algo */
   PSIM_OPT_FUSED_STEP = 1,      /* 1: force+kick+drift in one kernel (default), 0: separate kernels */
   PSIM_OPT_KERNEL_TIMING = 2,   /* 1: bracket every force-kernel launch with CUDA events */
-  PSIM_OPT_EXACT_DIFF_FILTER = 3, /* all-pairs kernel variant.
-                                    0 (default) and 3: distance filter on the tensor cores (tcgen05.mma kind::tf32
-                                      on split operands, TMEM accumulators, TMA-fed), exact pair arithmetic on the
-                                      CUDA cores for the few pairs that pass;
-                                    5: warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in
-                                      packed FP32 (3 FMAs per ordered pair) - the default before the tensor-core
-                                      kernel, 1.35-3x slower;
-                                    1: first-generation kernel with the distance test in difference form (3 sub,
-                                      1 mul, 2 FMA, 1 compare per pair: the literal reading of stoermer:117-121);
-                                    2: first-generation kernel with the pre-filter;
-                                    4: first, lock-step tensor-core kernel (kept for comparison);
-                                    6: EXPERIMENTAL tensor-core kernel with software-pipelined consumers (measured
-                                      1.26x faster than 0, but one intermittent launch failure was seen and its fix
-                                      is unverified: csrc/psim_allpairs_tc3.cuh). Not for production use yet.
-                                    All variants evaluate the same pairs with the same arithmetic; results differ
-                                    by summation order only. */
+  PSIM_OPT_ALLPAIRS_KERNEL = 3, /* psim_allpairs_kernel */
+  PSIM_OPT_EXACT_DIFF_FILTER = 3 /* round-1 name of PSIM_OPT_ALLPAIRS_KERNEL (same value; kept for callers built against it) */
 } psim_option;
 
 typedef struct psim_counters {
@@ -103,6 +104,10 @@ typedef struct psim_counters {
                              * sent through its exact path; tracked by the tensor-core all-pairs kernel only
                              * (-1 otherwise).  Equal to psim_count_pairs_in_range at the same positions iff
                              * the distance filter dropped no pair: the conservativeness check of the tests. */
+  int64_t filter_tests;     /* ordered pair distance tests of the last force launch over this handle's i-slice:
+                             * (owned i) x (n - 1) for an all-pairs kernel; for the cell-binned path the tests its
+                             * 27-cell neighbourhoods needed, counted only while PSIM_OPT_KERNEL_TIMING is on
+                             * (-1 otherwise).  bench.py's roofline accounting uses it. */
 } psim_counters;
 
 typedef struct psim_sim psim_sim;   /* opaque */
@@ -258,6 +263,13 @@ psim_status psim_compute_locations_static(const psim_params* params, int precisi
  * clock64() over the run. */
 psim_status psim_measure_fma_peak(int precision, int device, double* tflops,
                                   double* sm_mhz);
+
+/* Dense tcgen05.mma rate of this GPU in TFLOP/s: one issuing thread per SM on all
+ * SMs, M128 N256 instructions back to back into two TMEM accumulators.  kind 0 =
+ * kind::tf32 (K = 8 per instruction, what the default all-pairs kernel issues),
+ * kind 1 = kind::f16 (K = 16).  The roofline denominator of the tensor-core
+ * kernel (MEASURED_PEAKS.json has a cuBLAS bf16 figure only). */
+psim_status psim_measure_tensor_peak(int kind, int device, double* tflops, double* sm_mhz);
 
 const char* psim_status_string(int status);
 /* Text of the last CUDA/NCCL error seen by this thread ("" if none). */

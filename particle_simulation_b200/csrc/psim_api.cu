@@ -16,14 +16,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include "psim_allpairs.cuh"
 #include "psim_allpairs2.cuh"
 #include "psim_allpairs_tc.cuh"
-#include "psim_allpairs_tc2.cuh"
-#include "psim_allpairs_tc3.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -50,8 +49,16 @@ struct NcclApi {
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  std::once_flag once;
+  bool ok = false;
+  std::string why;
+  // Hosts may drive several handles from several threads: bind exactly once.
   bool load() {
-    if (so) return true;
+    std::call_once(once, [this] { ok = load_once(); if (!ok) why = g_last_error; });
+    if (!ok) g_last_error = why;
+    return ok;
+  }
+  bool load_once() {
     const char* names[] = {"libnccl.so.2", "libnccl.so"};
     for (const char* nm : names) {
       so = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
@@ -152,7 +159,8 @@ class SimT final : public psim_sim {
   static constexpr int RI = 2;                                    // i-particles per thread
   static constexpr int TS = 256;                                  // threads of the streaming kernels
   static constexpr int MAX_CLUSTER = 8;                           // portable cluster size limit
-  int variant = 0;      // 0 / 3: tensor-core filter kernel (default), 5: FFMA2 warp kernel, 1 / 2: v1 kernels, 4: lock-step tensor-core kernel, 6: experimental pipelined tensor-core kernel
+  int variant = PSIM_ALLPAIRS_TENSOR;   // psim_allpairs_kernel
+  int jsplit_forced = 0;                // PSIM_JSPLIT: j segments per i-block of the tensor-core kernel (0 = choose)
   int ri_sel = 0;       // force i-particles per lane of the production all-pairs kernel (6, 7, 8; 0 = choose)
   int cluster_forced = 0;
   int warps_forced = 0;
@@ -178,6 +186,11 @@ class SimT final : public psim_sim {
   unsigned char* tmp_active = nullptr;
   unsigned char* tc_bops = nullptr;     // tensor-core variant: B operand tiles of all particles
   unsigned long long* tc_pairs = nullptr;  // ... and the in-range pair count of its last launch (psim_counters.filter_pairs)
+  R* tc_part = nullptr;                 // ... j-split: partial forces [grid][3][128]
+  unsigned* tc_arrived = nullptr;       // ... j-split: arrival counter per i-block (zero between launches)
+  int64_t tc_part_cap = 0;
+  double* red_scratch = nullptr;        // 8 doubles: reductions of count_pairs / energy (no allocation per call)
+  bool attr_tc[3] = {false, false, false};
   CellPath<R> cells;
   // options
   int algo = PSIM_FORCE_ALL_PAIRS;
@@ -212,8 +225,8 @@ class SimT final : public psim_sim {
     for (auto& e : ev_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     ev_pool.clear();
     cudaFree(pos[0]); cudaFree(pos[1]); cudaFree(vel); cudaFree(f_old); cudaFree(f_new); cudaFree(disp);
-    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active); cudaFree(tc_bops); cudaFree(tc_pairs);
-    tc_bops = nullptr; tc_pairs = nullptr;
+    cudaFree(top2_part); cudaFree(top2_rank); cudaFree(ctrl); cudaFree(tmp3); cudaFree(tmp_active); cudaFree(tc_bops); cudaFree(tc_pairs); cudaFree(tc_part); cudaFree(tc_arrived); cudaFree(red_scratch);
+    tc_bops = nullptr; tc_pairs = nullptr; tc_part = nullptr; tc_arrived = nullptr; red_scratch = nullptr; tc_part_cap = 0;
     pos[0] = pos[1] = vel = f_old = f_new = disp = nullptr;
     top2_part = top2_rank = nullptr; ctrl = nullptr; tmp3 = nullptr; tmp_active = nullptr;
     if (stream) cudaStreamDestroy(stream);
@@ -239,6 +252,7 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
     if (const char* e = std::getenv("PSIM_RI")) { const int v = std::atoi(e); if (v >= 6 && v <= 8) ri_sel = v; }   // tuning knobs
     if (const char* e = std::getenv("PSIM_WARPS")) { const int v = std::atoi(e); if (v == 4 || v == 8 || v == 16) warps_forced = v; }
+    if (const char* e = std::getenv("PSIM_JSPLIT")) { const int v = std::atoi(e); if (v >= 1 && v <= tc::MAX_JSPLIT) jsplit_forced = v; }
     if (const char* e = std::getenv("PSIM_CLUSTER")) {
       const int v = std::atoi(e);
       if (v >= 1 && v <= MAX_CLUSTER) cluster_forced = v;
@@ -262,9 +276,13 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMalloc(&pos[0], rec)); PSIM_CK(cudaMalloc(&pos[1], rec));
     PSIM_CK(cudaMalloc(&vel, rec)); PSIM_CK(cudaMalloc(&f_old, rec));
     PSIM_CK(cudaMalloc(&f_new, rec)); PSIM_CK(cudaMalloc(&disp, rec));
-    top2_cap = std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 32 * 6) * MAX_CLUSTER) + 8;   // most blocks any drift-producing kernel launches
+    // most blocks any drift-producing kernel launches (tensor-core kernel: i-blocks x j segments)
+    top2_cap = std::max<int64_t>(std::max<int64_t>(blocks(n_pad, 64), blocks(n_pad, 32 * 6) * MAX_CLUSTER),
+                                 blocks(shard, tc::M) * tc::MAX_JSPLIT) + 8;
     PSIM_CK(cudaMalloc(&top2_part, sizeof(R) * 2 * top2_cap));
-    PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * world));
+    PSIM_CK(cudaMalloc(&top2_rank, sizeof(R) * 2 * c.slices * world));   // [world][slices][2]
+    PSIM_CK(cudaMemsetAsync(top2_rank, 0, sizeof(R) * 2 * c.slices * world, stream));
+    PSIM_CK(cudaMalloc(&red_scratch, 8 * sizeof(double)));
     PSIM_CK(cudaMalloc(&ctrl, sizeof(Control)));
     PSIM_CK(cudaMemsetAsync(ctrl, 0, sizeof(Control), stream));
     PSIM_CK(cudaMalloc(&tmp3, sizeof(R) * 3 * n_pad));
@@ -293,8 +311,7 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaMemcpyAsync(tmp3, pos_h, sizeof(R) * 3 * n, cudaMemcpyHostToDevice, stream));
     if (active_h) PSIM_CK(cudaMemcpyAsync(tmp_active, active_h, (size_t)n, cudaMemcpyHostToDevice, stream));
     init_positions_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(pos[0], pos[1], tmp3,
-                                                                     active_h ? tmp_active : nullptr,
-                                                                     cells.orig_or_null(), n, n_pad, c);
+                                                                     active_h ? tmp_active : nullptr, n, n_pad, c);
     unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(disp, nullptr, n, n_pad);
     unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(f_old, nullptr, n, n_pad);
     unpack3_kernel<R, TS><<<blocks(n_pad, TS), TS, 0, stream>>>(f_new, nullptr, n, n_pad);
@@ -312,17 +329,29 @@ class SimT final : public psim_sim {
     a.pos_cur = pos[cur]; a.pos_nxt = pos[cur ^ 1];
     a.vel = vel; a.f_old = f_old; a.f_new = f_new; a.disp = disp;
     a.top2_part = top2_part;
-    a.rank_pair = top2_rank + 2 * rank;
+    a.rank_pair = top2_rank + 2 * c.slices * rank;   // slices > 1: overwritten per slice by slice_top2_kernel
     a.ticket = &ctrl->ticket;
     a.n_pad = n_pad; a.i_lo = i_lo; a.i_hi = i_hi;
     a.c = c;
     return a;
   }
 
-  template <int MODE>
-  void launch_v1(const StepArgs<R>& a, int64_t grid) {
-    if (variant == 1) allpairs_step_kernel<R, T, RI, MODE, true><<<grid, T, 0, stream>>>(a);
-    else allpairs_step_kernel<R, T, RI, MODE, false><<<grid, T, 0, stream>>>(a);
+  // j segments per i-block of the tensor-core kernel: a block is 128 rows (the MMA's M), one block per SM,
+  // so a launch with few i-blocks (a shard, a small N) leaves SMs idle in its last wave; cutting j into S
+  // segments multiplies the blocks.  The smallest S that fills the waves wins (each block pays a fixed
+  // set-up, and the segments meet through global scratch).
+  int pick_jsplit(int64_t iblocks) const {
+    const int nt8 = (int)(n_pad / (8 * tc::N2));
+    const int smax = std::max(1, std::min(tc::MAX_JSPLIT, nt8));
+    if (jsplit_forced) return std::min(jsplit_forced, smax);
+    int best = 1;
+    double best_eff = -1.0;
+    for (int S = 1; S <= smax; ++S) {
+      const int64_t g = iblocks * S, waves = (g + sm_count - 1) / sm_count;
+      const double eff = (double)g / (double)(waves * sm_count) * (1.0 - 0.004 * (S - 1));
+      if (eff > best_eff + 1e-9) { best_eff = eff; best = S; }
+    }
+    return best;
   }
 
   // Tiling of the production all-pairs kernel: RI i-particles per lane (i-tile = 32 RI), W warps
@@ -362,11 +391,9 @@ class SimT final : public psim_sim {
     const int64_t itiles = blocks(i_hi - i_lo, 32 * RIv);
     auto kern = allpairs_warp_kernel<R, RIv, Wv, MODE>;
     constexpr size_t smem = allpairs_warp_smem<R, RIv, Wv>();
-    static bool attr_set[64] = {false};
-    if (!attr_set[device & 63]) {   // static tiles + dynamic accumulators can exceed the 48 KB default
+    {   // static tiles + dynamic accumulators can exceed the 48 KB default (a host-side call, no shared state)
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
-      attr_set[device & 63] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(itiles * S));
@@ -390,52 +417,41 @@ class SimT final : public psim_sim {
 
   template <int MODE>
   psim_status launch_allpairs(const StepArgs<R>& a, int64_t* grid_out) {
-    if (variant == 0 || variant == 3) {   // distance filter on the tensor cores (tcgen05 + TMEM), warp-specialised: the default
-      *grid_out = blocks(i_hi - i_lo, tc::M);
+    if (variant == PSIM_ALLPAIRS_TENSOR) {   // distance filter on the tensor cores (tcgen05 + TMEM): the default
+      const int64_t iblocks = blocks(i_hi - i_lo, tc::M);
+      tc::JSplit<R> js;
+      js.S = pick_jsplit(iblocks); js.part = nullptr; js.arrived = nullptr;
+      *grid_out = iblocks * js.S;
       if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
       if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
+      if (js.S > 1) {
+        if (tc_part_cap < *grid_out) {
+          cudaFree(tc_part); tc_part = nullptr;
+          PSIM_CK(cudaMalloc(&tc_part, sizeof(R) * 3 * tc::M * (size_t)*grid_out));
+          tc_part_cap = *grid_out;
+        }
+        if (!tc_arrived) {
+          const size_t cnt = (size_t)blocks(shard, tc::M) + 1;
+          PSIM_CK(cudaMalloc(&tc_arrived, sizeof(unsigned) * cnt));
+          PSIM_CK(cudaMemsetAsync(tc_arrived, 0, sizeof(unsigned) * cnt, stream));
+        }
+        js.part = tc_part; js.arrived = tc_arrived;
+      }
       tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, tc_pairs);
       ++launches;
-      // ring of B tiles + candidate queues (128 KB): also guarantees ONE block per SM — a block
-      // allocates all 512 TMEM columns, and no second block should ever wait inside tcgen05.alloc
+      // ring of B tiles + candidate queues (192 KB): also guarantees ONE block per SM — a block allocates
+      // all 512 TMEM columns, and no second block should ever wait inside tcgen05.alloc
       constexpr int kSmem = tc::SMEM_BYTES;
-      static bool attr_set[64] = {false};
-      if (!attr_set[device & 63]) {
-        PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tcws_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        attr_set[device & 63] = true;
+      if (!attr_tc[MODE]) {
+        PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tc_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_tc[MODE] = true;
       }
-      tc::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs);
+      tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs, js);
       return PSIM_OK;
     }
-    if (variant == 6) {          // EXPERIMENTAL: pipelined consumers (psim_allpairs_tc3.cuh); opt-in until verified
-      *grid_out = blocks(i_hi - i_lo, tc::M);
-      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
-      if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
-      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, tc_pairs);
-      ++launches;
-      constexpr int kSmem = tcp::SMEM_BYTES;
-      static bool attr_set[64] = {false};
-      if (!attr_set[device & 63]) {
-        PSIM_CK(cudaFuncSetAttribute(tcp::allpairs_tcws_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        attr_set[device & 63] = true;
-      }
-      tcp::allpairs_tcws_kernel<R, MODE><<<(unsigned)*grid_out, tcp::TW, kSmem, stream>>>(a, tc_bops, tc_pairs);
-      return PSIM_OK;
-    }
-    if (variant == 4) {          // first, lock-step tensor-core version (kept for comparison)
-      *grid_out = blocks(i_hi - i_lo, tc::M);
-      constexpr int kPad = 120 * 1024;
-      static bool attr_set[64] = {false};
-      if (!attr_set[device & 63]) {
-        PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tc_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPad));
-        attr_set[device & 63] = true;
-      }
-      tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::T, kPad, stream>>>(a);
-      return PSIM_OK;
-    }
-    if (variant != 5) {
+    if (variant == PSIM_ALLPAIRS_DIFFERENCE_FORM) {   // the literal reading of stoermer:117-121 in the working precision
       *grid_out = blocks(i_hi - i_lo, T * RI);
-      launch_v1<MODE>(a, *grid_out);
+      allpairs_step_kernel<R, T, RI, MODE, true><<<*grid_out, T, 0, stream>>>(a);
       return PSIM_OK;
     }
     const Tiling t = pick_tiling();
@@ -492,8 +508,7 @@ class SimT final : public psim_sim {
   // One cooperative launch: trigger, rebuild side effects, (cell path) re-binning and the
   // cell-ordered position copy.  pos_new is the buffer that is current from here on.
   int house_grid_max = 0;
-  psim_status launch_housekeeping(Real4<R>* pos_new, Real4<R>* pos_other, bool with_trigger, bool force_rebin,
-                                  bool flag_in_ctrl = false) {
+  psim_status launch_housekeeping(Real4<R>* pos_new, Real4<R>* pos_other, bool with_trigger, bool force_rebin) {
     if (!house_grid_max) {
       int per_sm = 0;
       PSIM_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, housekeeping_kernel<R>, 256, 0));
@@ -502,7 +517,7 @@ class SimT final : public psim_sim {
     HouseArgs<R> h = {};
     h.pos_new = pos_new; h.pos_other = pos_other; h.disp = disp;
     h.rank_pairs = with_trigger ? top2_rank : nullptr;
-    h.world = world; h.flag_in_ctrl = flag_in_ctrl ? 1 : 0;
+    h.world = world;
     h.ctrl = ctrl; h.parity = parity;
     h.n = n; h.i_lo = i_lo; h.i_hi = i_hi; h.c = c;
     h.cells = (algo == PSIM_FORCE_CELL_BINNED && cells.allocated()) ? 1 : 0;
@@ -519,20 +534,22 @@ class SimT final : public psim_sim {
   // After x_{n+1} of the owned slice is in pos[cur^1]: exchange (sharded), then housekeeping, swap.
   psim_status finish_drift() {
     Real4<R>* nxt = pos[cur ^ 1];
-    if (i_hi <= i_lo) PSIM_CK(cudaMemsetAsync(top2_rank + 2 * rank, 0, 2 * sizeof(R), stream));   // nothing owned
-    bool flag_in_ctrl = false;
+    const int ns = c.slices;
+    R* mine = top2_rank + 2 * ns * rank;
+    if (i_hi <= i_lo) PSIM_CK(cudaMemsetAsync(mine, 0, 2 * ns * sizeof(R), stream));   // nothing owned
+    else if (ns > 1) {
+      // NB_OF_THREADS > 1: the reference's per-slice trigger (program:71,86,92) over the part of every
+      // slice this handle owns; sharded handles exchange the per-slice pairs below.
+      slice_top2_kernel<R><<<ns, 256, 0, stream>>>(nxt, disp, n, i_lo, i_hi, mine, c);
+      ++launches;
+    }
     if (world > 1) {
       PSIM_NCCL(g_nccl.GroupStart());
       PSIM_NCCL(g_nccl.AllGather(nxt + shard * rank, nxt, (size_t)shard * 4, NcclType<R>::v, comm, stream));
-      PSIM_NCCL(g_nccl.AllGather(top2_rank + 2 * rank, top2_rank, 2, NcclType<R>::v, comm, stream));
+      PSIM_NCCL(g_nccl.AllGather(mine, top2_rank, (size_t)2 * ns, NcclType<R>::v, comm, stream));
       PSIM_NCCL(g_nccl.GroupEnd());
-    } else if (c.slices > 1) {
-      // NB_OF_THREADS > 1: the reference's per-slice trigger (single GPU)
-      slice_trigger_kernel<R><<<c.slices, 256, 0, stream>>>(nxt, disp, nullptr, n, ctrl, parity, c);
-      ++launches;
-      flag_in_ctrl = true;
     }
-    psim_status st = launch_housekeeping(nxt, pos[cur], true, false, flag_in_ctrl);
+    psim_status st = launch_housekeeping(nxt, pos[cur], true, false);
     if (st != PSIM_OK) return st;
     parity ^= 1;
     cur ^= 1;
@@ -548,7 +565,7 @@ class SimT final : public psim_sim {
         if (i_hi > i_lo) {
           const int64_t grid = blocks(i_hi - i_lo, TS);
           drift_kernel<R, TS><<<grid, TS, 0, stream>>>(pos[cur], pos[cur ^ 1], vel, f_old, f_new, disp, top2_part,
-                                                       &ctrl->ticket, top2_rank + 2 * rank, i_lo, i_hi, c);
+                                                       &ctrl->ticket, top2_rank + 2 * c.slices * rank, i_lo, i_hi, c);
           ++launches;
         }
       }
@@ -576,18 +593,20 @@ class SimT final : public psim_sim {
 
   psim_status advance_timed(int64_t nsteps, double* ms) override {
     PSIM_CK(cudaSetDevice(device));
-    cudaEvent_t a, b;
-    PSIM_CK(cudaEventCreate(&a)); PSIM_CK(cudaEventCreate(&b));
+    struct Events {                                 // released on every return path
+      cudaEvent_t a = nullptr, b = nullptr;
+      ~Events() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    } ev;
+    PSIM_CK(cudaEventCreate(&ev.a)); PSIM_CK(cudaEventCreate(&ev.b));
     PSIM_CK(cudaStreamSynchronize(stream));
-    PSIM_CK(cudaEventRecord(a, stream));
+    PSIM_CK(cudaEventRecord(ev.a, stream));
     psim_status st = advance(nsteps);
     if (st != PSIM_OK) return st;
-    PSIM_CK(cudaEventRecord(b, stream));
-    PSIM_CK(cudaEventSynchronize(b));
+    PSIM_CK(cudaEventRecord(ev.b, stream));
+    PSIM_CK(cudaEventSynchronize(ev.b));
     float f = 0;
-    PSIM_CK(cudaEventElapsedTime(&f, a, b));
+    PSIM_CK(cudaEventElapsedTime(&f, ev.a, ev.b));
     if (ms) *ms = f;
-    cudaEventDestroy(a); cudaEventDestroy(b);
     return PSIM_OK;
   }
 
@@ -600,7 +619,7 @@ class SimT final : public psim_sim {
 
   psim_status fetch3(void* host, const Real4<R>* src, int64_t lo, int64_t hi) {
     if (!host || hi <= lo) return PSIM_OK;
-    pack3_kernel<R, TS><<<blocks(hi - lo, TS), TS, 0, stream>>>(tmp3, src, cells.orig_or_null(), lo, hi); ++launches;
+    pack3_kernel<R, TS><<<blocks(hi - lo, TS), TS, 0, stream>>>(tmp3, src, lo, hi); ++launches;
     PSIM_CK(cudaMemcpyAsync((R*)host + 3 * lo, tmp3 + 3 * lo, sizeof(R) * 3 * (hi - lo), cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     return PSIM_OK;
@@ -614,7 +633,7 @@ class SimT final : public psim_sim {
     st = fetch3(vel_h, vel, i_lo, i_hi);
     if (st != PSIM_OK) return st;
     if (active_h) {
-      pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(tmp_active, pos[cur], cells.orig_or_null(), n, c, ctrl); ++launches;
+      pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(tmp_active, pos[cur], n, c, ctrl); ++launches;
       PSIM_CK(cudaMemcpyAsync(active_h, tmp_active, (size_t)n, cudaMemcpyDeviceToHost, stream));
       PSIM_CK(cudaStreamSynchronize(stream));
     }
@@ -636,14 +655,22 @@ class SimT final : public psim_sim {
     psim_status st = drain_events();
     if (st != PSIM_OK) return st;
     PSIM_CK(cudaMemsetAsync(&ctrl->n_active, 0, sizeof(unsigned long long), stream));
-    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nullptr, pos[cur], nullptr, n, c, ctrl); ++launches;
+    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(nullptr, pos[cur], n, c, ctrl); ++launches;
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
     unsigned long long fp = 0;
-    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && (variant == 0 || variant == 3 || variant == 6) && tc_pairs;
+    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && variant == PSIM_ALLPAIRS_TENSOR && tc_pairs;
     if (tracked) PSIM_CK(cudaMemcpyAsync(&fp, tc_pairs, sizeof fp, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     out->filter_pairs = tracked ? (int64_t)fp : -1;
+    out->filter_tests = -1;
+    if (algo == PSIM_FORCE_ALL_PAIRS) out->filter_tests = (i_hi - i_lo) * (n - 1);
+    else if (cells.tested && timing) {
+      unsigned long long ft = 0;
+      PSIM_CK(cudaMemcpyAsync(&ft, cells.tested, sizeof ft, cudaMemcpyDeviceToHost, stream));
+      PSIM_CK(cudaStreamSynchronize(stream));
+      out->filter_tests = (int64_t)ft;
+    }
     out->steps = steps;
     out->rebuilds = (int64_t)h.rebuilds;
     out->kernel_launches = launches + cells.launches;
@@ -661,8 +688,11 @@ class SimT final : public psim_sim {
         algo = (int)value; cells.invalidate(); return PSIM_OK;
       case PSIM_OPT_FUSED_STEP: fused = value != 0; return PSIM_OK;
       case PSIM_OPT_KERNEL_TIMING: timing = value != 0; return PSIM_OK;
-      case PSIM_OPT_EXACT_DIFF_FILTER:
-        if (value < 0 || value > 6) return PSIM_ERR_INVALID_ARGUMENT;
+      case PSIM_OPT_ALLPAIRS_KERNEL:
+        // 3 and 6 selected the round-1 tensor-core kernels: both are today's default
+        if (value == 3 || value == 6) value = PSIM_ALLPAIRS_TENSOR;
+        if (value != PSIM_ALLPAIRS_TENSOR && value != PSIM_ALLPAIRS_DIFFERENCE_FORM && value != PSIM_ALLPAIRS_CUDA_CORE)
+          return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
     }
@@ -690,10 +720,9 @@ class SimT final : public psim_sim {
     if (st != PSIM_OK) return st;
     if (s.used) PSIM_CK(cudaStreamWaitEvent(stream, s.done, 0));   // previous drain of this slot
     // while a fused kernel has already drifted, pos[cur] still holds x_n
-    const int32_t* og = cells.orig_or_null();
-    pack3_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_pos, pos[cur], og, 0, n);
-    if (i_hi > i_lo) pack3_kernel<R, TS><<<blocks(i_hi - i_lo, TS), TS, 0, stream>>>(s.d_vel, vel, og, i_lo, i_hi);
-    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_act, pos[cur], og, n, c, ctrl);
+    pack3_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_pos, pos[cur], 0, n);
+    if (i_hi > i_lo) pack3_kernel<R, TS><<<blocks(i_hi - i_lo, TS), TS, 0, stream>>>(s.d_vel, vel, i_lo, i_hi);
+    pack_active_kernel<R, TS><<<blocks(n, TS), TS, 0, stream>>>(s.d_act, pos[cur], n, c, ctrl);
     launches += 3;
     PSIM_CK(cudaEventRecord(s.ready, stream));
     PSIM_CK(cudaStreamWaitEvent(side, s.ready, 0));
@@ -722,8 +751,7 @@ class SimT final : public psim_sim {
 
   psim_status count_pairs(int64_t* pairs) override {
     PSIM_CK(cudaSetDevice(device));
-    unsigned long long* d = nullptr;
-    PSIM_CK(cudaMalloc(&d, sizeof *d));
+    unsigned long long* d = reinterpret_cast<unsigned long long*>(red_scratch);
     PSIM_CK(cudaMemsetAsync(d, 0, sizeof *d, stream));
     if (i_hi > i_lo) {
       count_pairs_kernel<R, 128><<<blocks(i_hi - i_lo, 128), 128, 0, stream>>>(pos[cur], n_pad, i_lo, i_hi, c, d);
@@ -732,15 +760,13 @@ class SimT final : public psim_sim {
     unsigned long long h = 0;
     PSIM_CK(cudaMemcpyAsync(&h, d, sizeof h, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
-    cudaFree(d);
     if (pairs) *pairs = (int64_t)h;
     return PSIM_OK;
   }
 
   psim_status energy(double* k, double* u, double* mom) override {
     PSIM_CK(cudaSetDevice(device));
-    double* d = nullptr;
-    PSIM_CK(cudaMalloc(&d, 5 * sizeof(double)));
+    double* d = red_scratch;
     PSIM_CK(cudaMemsetAsync(d, 0, 5 * sizeof(double), stream));
     if (i_hi > i_lo) {
       energy_kernel<R, 128><<<blocks(i_hi - i_lo, 128), 128, 0, stream>>>(pos[cur], vel, n_pad, i_lo, i_hi, c, mass, d);
@@ -749,7 +775,6 @@ class SimT final : public psim_sim {
     double h[5];
     PSIM_CK(cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
-    cudaFree(d);
     if (k) *k = h[0];
     if (u) *u = h[1];
     if (mom) { mom[0] = h[2]; mom[1] = h[3]; mom[2] = h[4]; }
@@ -820,6 +845,90 @@ static psim_status fma_peak_t(int device, double* tflops, double* sm_mhz) {
     }
   }
   cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out); cudaFree(cyc);
+  PSIM_CK(cudaGetLastError());
+  if (tflops) *tflops = best;
+  if (sm_mhz) *sm_mhz = best_mhz;
+  return PSIM_OK;
+}
+
+// Dense tcgen05.mma rate: one thread per SM issues `iters` M128 N256 instructions back to back into two
+// alternating TMEM accumulators (operands: zeros in the canonical no-swizzle K-major layout, 32 B rows) and
+// commits once at the end.  KIND 0: kind::tf32, K = 8; 1: kind::f16, K = 16.
+template <int KIND>
+__global__ void __launch_bounds__(32) tensor_peak_kernel(long long* cycles, int iters) {
+  constexpr int MM = 128, NN = 256;
+  __shared__ __align__(128) unsigned char sA[MM * 32];
+  __shared__ __align__(128) unsigned char sB[NN * 32];
+  __shared__ __align__(8) unsigned long long mbar;
+  __shared__ unsigned tmem_base;
+  const int tid = threadIdx.x;
+  for (int e = tid; e < MM * 32 / 4; e += 32) reinterpret_cast<unsigned*>(sA)[e] = 0u;
+  for (int e = tid; e < NN * 32 / 4; e += 32) reinterpret_cast<unsigned*>(sB)[e] = 0u;
+  if (tid == 0) {
+    tc::mbar_init(tc::smem_u32(&mbar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(tc::smem_u32(&tmem_base)));
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  const unsigned tm = tmem_base;
+  if (tid == 0) {
+    const unsigned fmt = KIND == 0 ? ((2u << 7) | (2u << 10)) : 0u;     // a/b format: TF32 = 2, F16 = 0; D = F32
+    const unsigned idesc = (1u << 4) | fmt | ((unsigned)(NN >> 3) << 17) | ((unsigned)(MM >> 4) << 24);
+    const unsigned long long da = tc::make_desc(tc::smem_u32(sA)), db = tc::make_desc(tc::smem_u32(sB));
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+      const unsigned acc = tm + (unsigned)((it & 1) * NN);
+      if (KIND == 0)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
+                     :: "r"(acc), "l"(da), "l"(db), "r"(idesc), "r"(1u), "r"(0u), "r"(0u), "r"(0u), "r"(0u));
+      else
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
+                     :: "r"(acc), "l"(da), "l"(db), "r"(idesc), "r"(1u), "r"(0u), "r"(0u), "r"(0u), "r"(0u));
+    }
+    tc::umma_commit(tc::smem_u32(&mbar));
+    tc::mbar_wait(tc::smem_u32(&mbar), 0u);
+    cycles[blockIdx.x] = clock64() - t0;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tm));
+}
+
+static psim_status tensor_peak(int kind, int device, double* tflops, double* sm_mhz) {
+  PSIM_CK(cudaSetDevice(device));
+  int nsm = 0;
+  PSIM_CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
+  struct Res {                                      // released on every return path
+    long long* cyc = nullptr; cudaEvent_t a = nullptr, b = nullptr;
+    ~Res() { cudaFree(cyc); if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+  } r;
+  PSIM_CK(cudaMalloc(&r.cyc, sizeof(long long) * nsm));
+  PSIM_CK(cudaEventCreate(&r.a)); PSIM_CK(cudaEventCreate(&r.b));
+  const int iters = 20000;
+  double best = 0, best_mhz = 0;
+  for (int rep = 0; rep < 4; ++rep) {
+    PSIM_CK(cudaEventRecord(r.a, 0));
+    if (kind == 0) tensor_peak_kernel<0><<<nsm, 32>>>(r.cyc, iters);
+    else tensor_peak_kernel<1><<<nsm, 32>>>(r.cyc, iters);
+    PSIM_CK(cudaEventRecord(r.b, 0));
+    PSIM_CK(cudaEventSynchronize(r.b));
+    float ms = 0;
+    PSIM_CK(cudaEventElapsedTime(&ms, r.a, r.b));
+    const double flops = 2.0 * 128 * 256 * (kind == 0 ? 8 : 16) * (double)iters * nsm;
+    const double tf = flops / (ms * 1e-3) / 1e12;
+    if (rep >= 1 && tf > best) {
+      best = tf;
+      long long h = 0;
+      PSIM_CK(cudaMemcpy(&h, r.cyc, sizeof h, cudaMemcpyDeviceToHost));
+      best_mhz = (double)h / (ms * 1e-3) / 1e6;
+    }
+  }
   PSIM_CK(cudaGetLastError());
   if (tflops) *tflops = best;
   if (sm_mhz) *sm_mhz = best_mhz;
@@ -903,6 +1012,14 @@ psim_status psim_measure_fma_peak(int precision, int device, double* tflops, dou
   if (precision == 4) return fma_peak_t<float>(device, tflops, sm_mhz);
   if (precision == 8) return fma_peak_t<double>(device, tflops, sm_mhz);
   return PSIM_ERR_INVALID_ARGUMENT;
+}
+
+psim_status psim_measure_tensor_peak(int kind, int device, double* tflops, double* sm_mhz) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return PSIM_ERR_NO_DEVICE; }
+  if (device < 0) device = 0;
+  if (kind != 0 && kind != 1) return PSIM_ERR_INVALID_ARGUMENT;
+  return tensor_peak(kind, device, tflops, sm_mhz);
 }
 
 const char* psim_status_string(int status) {

@@ -21,7 +21,9 @@ from . import build as _build
 
 STATUS_OK = 0
 FORCE_ALL_PAIRS, FORCE_CELL_BINNED = 0, 1
-OPT_FORCE_ALGO, OPT_FUSED_STEP, OPT_KERNEL_TIMING, OPT_EXACT_DIFF_FILTER = 0, 1, 2, 3
+OPT_FORCE_ALGO, OPT_FUSED_STEP, OPT_KERNEL_TIMING, OPT_ALLPAIRS_KERNEL = 0, 1, 2, 3
+OPT_EXACT_DIFF_FILTER = OPT_ALLPAIRS_KERNEL      # round-1 name
+ALLPAIRS_TENSOR, ALLPAIRS_DIFFERENCE_FORM, ALLPAIRS_CUDA_CORE = 0, 1, 5
 FRAME_SLOTS = 4
 
 
@@ -52,6 +54,7 @@ class Counters(C.Structure):
         ("force_timed", C.c_int64),
         ("n_active", C.c_int64),
         ("filter_pairs", C.c_int64),
+        ("filter_tests", C.c_int64),
     ]
 
 
@@ -84,6 +87,7 @@ EXPORTS = (
     "psim_get_counters", "psim_get_shard", "psim_set_positions", "psim_snapshot_async", "psim_snapshot_wait",
     "psim_compute_forces_host", "psim_count_pairs_in_range", "psim_energy", "psim_measure_fma_peak",
     "psim_status_string", "psim_last_error", "psim_version", "psim_compute_locations_static",
+    "psim_measure_tensor_peak",
 )
 
 
@@ -124,6 +128,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         "psim_count_pairs_in_range": [vp, C.POINTER(i64)],
         "psim_energy": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "psim_measure_fma_peak": [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)],
+        "psim_measure_tensor_peak": [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "psim_compute_locations_static": [PP, i32, i64, vp, vp, vp, vp, vp, vp, vp, vp],
     }
     for name, args in sig.items():
@@ -336,4 +341,11 @@ def comm_unique_id() -> bytes:
 def measure_fma_peak(precision: int, device: int = 0):
     tf, mhz = C.c_double(), C.c_double()
     _check(load().psim_measure_fma_peak(precision, device, C.byref(tf), C.byref(mhz)), "psim_measure_fma_peak")
+    return tf.value, mhz.value
+
+
+def measure_tensor_peak(kind: int = 0, device: int = 0):
+    """Dense tcgen05.mma rate (TFLOP/s) and SM clock (MHz): kind 0 = kind::tf32, 1 = kind::f16."""
+    tf, mhz = C.c_double(), C.c_double()
+    _check(load().psim_measure_tensor_peak(kind, device, C.byref(tf), C.byref(mhz)), "psim_measure_tensor_peak")
     return tf.value, mhz.value

@@ -1,5 +1,5 @@
 """CPU check of the MATHEMATICS of the tensor-core distance filter (csrc/psim_allpairs_tc.cuh: filter_record_tc,
-split2 / split3, the K = 16 operand layout of psim_allpairs_tc2.cuh), restated in numpy.
+split2 / split3, the K = 16 operand layout of psim_allpairs_tc.cuh), restated in numpy.
 
 What it proves: for every ordered pair with true r < r_cut the filter estimate stays below the row's cut value
 even under a worst-case model of the tensor core's arithmetic — the products of the 11-bit TF32 pieces are exact
