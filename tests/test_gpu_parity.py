@@ -28,22 +28,21 @@ def _ref_files():
     return os.path.join(GOLDEN, "two_cubes_432.dat")
 
 
-ALGOS = ["allpairs", "allpairs_ffma2", "cells"]
+ALGOS = ["allpairs", "allpairs_cuda_core", "cells"]
+
+KERNEL = {"allpairs": 0, "allpairs_difference_form": 1, "allpairs_cuda_core": 5,
+          "allpairs_round1_alias_3": 3, "allpairs_round1_alias_6": 6}
 
 
 def _select(psim, sim, algo):
     sim.set_option(psim.OPT_FORCE_ALGO, psim.FORCE_CELL_BINNED if algo == "cells" else psim.FORCE_ALL_PAIRS)
-    if algo == "allpairs_ffma2":
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)
-
-
-# the experimental pipelined tensor-core kernel (value 6) is only exercised on request: one intermittent launch
-# failure was seen with it (csrc/psim_allpairs_tc3.cuh), and a failed launch poisons the CUDA context of the session
-EXPERIMENTAL = ["allpairs_tensor_pipelined"] if os.environ.get("PSIM_TEST_EXPERIMENTAL") == "1" else []
+    if algo in KERNEL:
+        sim.set_option(psim.OPT_ALLPAIRS_KERNEL, KERNEL[algo])
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("variant", ["allpairs", "allpairs_exact_diff", "allpairs_v1_filter", "allpairs_tensor", "allpairs_tensor_lockstep", "allpairs_ffma2", "cells"] + EXPERIMENTAL)
+@pytest.mark.parametrize("variant", ["allpairs", "allpairs_difference_form", "allpairs_cuda_core",
+                                     "allpairs_round1_alias_3", "allpairs_round1_alias_6", "cells"])
 def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     ids, pos, vel = two_cubes()
     p = psim.make_params()
@@ -51,27 +50,8 @@ def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     o = oracle.Oracle(op, precision, ids, pos, vel)
     _, _, f_ref = o.aux()
     sim = psim.Simulation(p, ids, pos, vel, precision)
-    if variant == "allpairs_exact_diff":
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 1)
-        sim.set_positions(pos)
-    elif variant == "allpairs_v1_filter":
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 2)
-        sim.set_positions(pos)
-    elif variant == "allpairs_tensor":                 # explicit; "allpairs" (value 0) selects the same kernel
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 3)
-        sim.set_positions(pos)
-    elif variant == "allpairs_tensor_lockstep":
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 4)
-        sim.set_positions(pos)
-    elif variant == "allpairs_ffma2":
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)
-        sim.set_positions(pos)
-    elif variant == "allpairs_tensor_pipelined":
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, 6)
-        sim.set_positions(pos)
-    elif variant.startswith("cells"):
-        _select(psim, sim, variant)
-        sim.set_positions(pos)
+    _select(psim, sim, variant)
+    sim.set_positions(pos)
     f = sim.forces()
     scale = np.abs(f_ref).max()
     assert scale > 0
@@ -80,6 +60,18 @@ def test_initial_forces_match_oracle(psim, oracle, precision, variant):
     bf, pairs = oracle.bruteforce(op, precision, pos)
     assert np.abs(f - bf).max() <= 4 * FTOL[precision] * scale
     assert sim.pairs_in_range() == pairs
+    if variant in ("allpairs", "allpairs_round1_alias_3", "allpairs_round1_alias_6"):
+        assert sim.counters().filter_pairs == pairs          # the tensor-core filter dropped no pair
+    sim.close()
+
+
+def test_removed_kernel_values_are_refused(psim):
+    ids, pos, vel = two_cubes(side=3)
+    sim = psim.Simulation(psim.make_params(), ids, pos, vel, 8)
+    for value in (2, 4, 7, -1):
+        with pytest.raises(psim.PsimError) as e:
+            sim.set_option(psim.OPT_ALLPAIRS_KERNEL, value)
+        assert e.value.status == 1
     sim.close()
 
 
@@ -163,49 +155,52 @@ def test_conservation_and_energy(psim, oracle, algo):
     ko, uo, po = o.energy()
     assert abs(k0 - ko) <= 1e-9 * abs(ko) and abs(u0 - uo) <= 1e-9 * abs(uo)
     sim.advance(400)
+    o.advance(400)
     k1, u1, p1 = sim.energy()
+    ko1, uo1, _ = o.energy()
     assert np.abs(p1 - p0).max() <= 1e-9 * np.abs(p0).max()          # momentum: pairwise antisymmetric forces
     assert abs((k1 + u1) - (k0 + u0)) <= 2e-5 * abs(k0 + u0)          # velocity Verlet, dt = 1e-3
+    # "total-energy drift matching" (north_star): the drift over the same 400 steps equals the oracle's
+    drift, drift_o = (k1 + u1) - (k0 + u0), (ko1 + uo1) - (ko + uo)
+    assert abs(drift - drift_o) <= 1e-9 * abs(ko + uo)
     sim.close()
+    o.close()
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("kernel", [0] + ([6] if EXPERIMENTAL else []))
-@pytest.mark.parametrize("case", ["lattice_65536", "hot_gas_32768", "two_cubes"])
-def test_tensor_core_filter_drops_no_pair(psim, precision, case, kernel):
+@pytest.mark.parametrize("case", ["lattice_65536", "hot_gas_32768", "two_cubes", "corner_of_big_box"])
+def test_tensor_core_filter_drops_no_pair(psim, oracle, precision, case):
     """The tensor-core distance filter (split-TF32 Gram matrix) must be conservative: the ordered in-range
     pairs its exact path evaluated (psim_counters.filter_pairs) equal the exact O(N^2) count, and stay equal
-    while the configuration moves.  The forces then agree with the default kernel's up to summation order
-    (both evaluate every pair with the same one-rounding-per-operation arithmetic)."""
+    while the configuration moves; the forces equal the CPU oracle's brute-force evaluation at the same
+    positions.  corner_of_big_box puts the block in the far corner of the 198 x 198 x 99 box of the
+    N = 1,048,576 configuration, where the filter's margins (which grow with the distance from the box
+    centre) are widest."""
     from particle_simulation_b200 import generate as G
+    kw = {}
     if case == "two_cubes":
         ids, pos, vel = two_cubes()
-        params = psim.make_params()
     elif case == "lattice_65536":
         ids, pos, vel, area = G.synthetic(65536)
-        params = psim.make_params(length_of_area=area)
+        kw = dict(length_of_area=area)
+    elif case == "corner_of_big_box":
+        ids, pos, vel = G.lattice_block((32, 32, 16), (177.0, 177.0, 88.0), thermal=0.1, seed=5)
+        kw = dict(length_of_area=(198.0, 198.0, 99.0))
     else:   # strongly perturbed lattice: many pairs close to the cut-off on both sides
         ids, pos, vel, area = G.synthetic(32768, thermal=0.1)
         rng = np.random.default_rng(11)
         pos = pos + rng.uniform(-0.45, 0.45, pos.shape)
         vel = vel * 0.0
-        params = psim.make_params(length_of_area=area, delta_t=1e-5)
-    ref = psim.Simulation(params, ids, pos, vel, precision)
-    ref.set_option(psim.OPT_EXACT_DIFF_FILTER, 5)        # the CUDA-core kernel
-    ref.set_positions(pos)
-    sim = psim.Simulation(params, ids, pos, vel, precision)   # default: the tensor-core kernel
-    if kernel:
-        sim.set_option(psim.OPT_EXACT_DIFF_FILTER, kernel)
-        sim.set_positions(pos)
+        kw = dict(length_of_area=area, delta_t=1e-5)
+    sim = psim.Simulation(psim.make_params(**kw), ids, pos, vel, precision)   # default: the tensor-core kernel
     for round_ in range(3):
         exact = sim.pairs_in_range()
         assert exact > 0
         assert sim.counters().filter_pairs == exact
-        assert ref.counters().filter_pairs == -1
-        f, f_ref = sim.forces(), ref.forces()
-        scale = np.abs(f_ref).max()
-        assert np.abs(f - f_ref).max() <= (1e-4 if precision == 4 else 1e-11) * scale
+        _, x, _, a = sim.frame()
+        bf, pairs = oracle.bruteforce(oracle.make_params(**kw), precision, x, a)
+        assert pairs == exact
+        f = sim.forces()
+        assert np.abs(f - bf).max() <= 4 * FTOL[precision] * np.abs(bf).max()
         sim.advance(7)
-        ref.advance(7)
     sim.close()
-    ref.close()
