@@ -33,47 +33,75 @@ def main():
         return bytes(buf.cpu().numpy().tobytes())
 
     ok = True
-    for precision, xtol, algo in ((8, 1e-9, "allpairs"), (4, 2e-4, "allpairs"), (8, 1e-9, "cells"), (4, 2e-4, "cells")):
-        for scenario in ("calm", "leaving"):
-            if scenario == "calm":
-                ids, pos, vel = two_cubes()
-                kw = {}
-            else:
-                ids, pos, vel = two_cubes(side=4, speed=40.0, origin=3.0)
-                kw = dict(length_of_area=(30.0, 30.0, 30.0), delta_t=0.002)
-            n = len(ids)
-            sim = P.Simulation(P.make_params(**kw), ids, pos, vel, precision, device=local, rank=rank, world=world,
-                               nccl_unique_id=fresh_uid())
-            assert (sim.i_lo, sim.i_hi) == sharding.shard_bounds(n, rank, world)
-            if algo == "cells":
-                sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
-            o = O.Oracle(O.make_params(**kw), precision, ids, pos, vel)
-            for chunk in (1, 30, 29):
-                sim.advance(chunk); o.advance(chunk)
-            _, x, v, a = sim.frame()
-            _, xr, vr, ar = o.frame()
-            # velocities: every rank fills its own slice; merge in rank order
-            parts = [torch.zeros((n, 3), dtype=torch.float64, device="cuda") for _ in range(world)]
-            dist.all_gather(parts, torch.from_numpy(v.astype(np.float64)).cuda())
-            bounds = [sharding.shard_bounds(n, r, world) for r in range(world)]
-            vm = sharding.merge_owned([p.cpu().numpy() for p in parts], bounds, n)
-            # the violent f32 scenario is chaotic beyond ~50 steps: flags and schedule only
-            compare_xv = not (scenario == "leaving" and precision == 4)
-            good = np.array_equal(a, ar) and sim.counters().rebuilds == o.rebuilds
-            keep = ar.astype(bool)      # ejected particles carry |x| ~ 1e10: compare the active ones
-            if compare_xv and keep.any():
-                good = good and np.abs(x[keep] - xr[keep]).max() <= 50 * xtol and np.abs(vm[keep] - vr[keep]).max() <= 5000 * xtol
-            if scenario == "leaving":
-                good = good and (ar == 0).any()
-            if not good:
-                ix = np.unravel_index(np.abs(x - xr).argmax(), x.shape); iv = np.unravel_index(np.abs(vm - vr).argmax(), vm.shape)
-                print("rank %d detail: x[%s]=%r ref %r act %d/%d | v[%s]=%r ref %r act %d/%d flags_equal=%s" % (
-                    rank, ix, x[ix], xr[ix], a[ix[0]], ar[ix[0]], iv, vm[iv], vr[iv], a[iv[0]], ar[iv[0]], np.array_equal(a, ar)), flush=True)
-                print("rank %d: MISMATCH algo=%s precision=%d scenario=%s dx=%g dv=%g rebuilds %d vs %d" % (
-                    rank, algo, precision, scenario, np.abs(x - xr).max(), np.abs(vm - vr).max(),
-                    sim.counters().rebuilds, o.rebuilds))
-            ok = ok and good
-            sim.close(); o.close()
+    cases = []
+    for precision, xtol in ((8, 1e-9), (4, 2e-4)):
+        for algo in ("allpairs", "cells"):
+            for scenario in ("calm", "leaving"):
+                for threads in (1, 3):        # NB_OF_THREADS: the reference's per-slice rebuild trigger (shipped: 3)
+                    cases.append((precision, xtol, algo, scenario, threads))
+    cases.append((8, 1e-9, "allpairs", "lattice_65536", 3))     # many i-blocks per rank, j-split, i_lo > 0
+    cases.append((8, 1e-9, "cells", "lattice_65536", 1))
+    for precision, xtol, algo, scenario, threads in cases:
+        if scenario == "calm":
+            ids, pos, vel = two_cubes()
+            kw = {}
+            chunks = (1, 30, 29)
+        elif scenario == "leaving":
+            ids, pos, vel = two_cubes(side=4, speed=40.0, origin=3.0)
+            kw = dict(length_of_area=(30.0, 30.0, 30.0), delta_t=0.002)
+            chunks = (1, 30, 29)
+        else:
+            from particle_simulation_b200 import generate as G
+            ids, pos, vel, area = G.synthetic(65536)
+            vel = vel + np.array([8.0, 0.0, 0.0])       # fast enough for a rebuild inside the horizon
+            kw = dict(length_of_area=area)
+            chunks = (1, 39)
+        kw["nb_of_threads"] = threads
+        n = len(ids)
+        sim = P.Simulation(P.make_params(**kw), ids, pos, vel, precision, device=local, rank=rank, world=world,
+                           nccl_unique_id=fresh_uid())
+        assert (sim.i_lo, sim.i_hi) == sharding.shard_bounds(n, rank, world)
+        if algo == "cells":
+            sim.set_option(P.OPT_FORCE_ALGO, P.FORCE_CELL_BINNED)
+            sim.set_positions(pos)
+        o = O.Oracle(O.make_params(**kw), precision, ids, pos, vel)
+        # forces at the start, owned slice
+        f0 = sim.forces(); f0r = o.aux()[2]
+        ftol = 1e-12 if precision == 8 else 1e-5
+        good = True
+        if sim.i_hi > sim.i_lo:
+            good = np.abs(f0[sim.i_lo:sim.i_hi] - f0r[sim.i_lo:sim.i_hi]).max() <= ftol * np.abs(f0r).max()
+        for chunk in chunks:
+            sim.advance(chunk); o.advance(chunk)
+        _, x, v, a = sim.frame()
+        _, xr, vr, ar = o.frame()
+        # velocities: every rank fills its own slice; merge in rank order
+        parts = [torch.zeros((n, 3), dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(parts, torch.from_numpy(v.astype(np.float64)).cuda())
+        bounds = [sharding.shard_bounds(n, r, world) for r in range(world)]
+        vm = sharding.merge_owned([p.cpu().numpy() for p in parts], bounds, n)
+        # the violent f32 scenario is chaotic beyond ~50 steps: flags and schedule only
+        compare_xv = not (scenario == "leaving" and precision == 4)
+        rebuilds = sim.counters().rebuilds
+        good = bool(good) and np.array_equal(a, ar) and rebuilds == o.rebuilds
+        keep = ar.astype(bool)      # ejected particles carry |x| ~ 1e10: compare the active ones
+        dx = np.abs(x[keep] - xr[keep]).max() if keep.any() else 0.0
+        dv = np.abs(vm[keep] - vr[keep]).max() if keep.any() else 0.0
+        if compare_xv:
+            good = good and dx <= 50 * xtol and dv <= 5000 * xtol
+        if scenario == "leaving":
+            good = good and (ar == 0).any()
+        if scenario == "lattice_65536":
+            good = good and rebuilds >= 1
+        if rank == 0:
+            print("%s algo=%s f%d scenario=%s NB_OF_THREADS=%d ranks=%d: rebuilds %d (oracle %d), inactive %d, dx=%.3g dv=%.3g" % (
+                "ok      " if good else "MISMATCH", algo, 8 * precision, scenario, threads, world, rebuilds, o.rebuilds,
+                int((ar == 0).sum()), dx, dv), flush=True)
+        elif not good:
+            print("rank %d: MISMATCH algo=%s precision=%d scenario=%s threads=%d dx=%g dv=%g rebuilds %d vs %d flags_equal=%s" % (
+                rank, algo, precision, scenario, threads, dx, dv, rebuilds, o.rebuilds, np.array_equal(a, ar)), flush=True)
+        ok = ok and good
+        sim.close(); o.close()
     t = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0 and t.item() == 1.0:
