@@ -173,7 +173,8 @@ FrameWriter::FrameWriter(const std::string& path, const double area[3], int nbyt
     if (nbytes_ == 4) { float v = (float)area[d]; std::fwrite(&v, 4, 1, f_); }
     else { double v = area[d]; std::fwrite(&v, 8, 1, f_); }
   }
-  put_int(0);                                                // record 4: frames so far
+  // record 4 (frames so far) is NOT written here: the reference writes it inside write_data only
+  // (:336-337), so a run with MAX_TIME_STEP < WRITE_TIME_STEP leaves a file of three records
 }
 
 FrameWriter::~FrameWriter() { close(); }

@@ -126,8 +126,10 @@ def write_particles(path: str, ids, pos, vel, append: bool = False):
 class OutputWriter:
     """The `.output` stream (program_...:54-56, 327-365): records of `nbytes`
     (4 as shipped; 8 when rt => real64, integers then occupy the low 4 bytes of
-    an 8-byte record).  Record 1-3 = length_of_area, record 4 = frames so far,
-    then per frame one count record (7 * n_active) and n_active * 7 records."""
+    an 8-byte record).  Record 1-3 = length_of_area, record 4 = frames so far
+    (written by write_data only, so a run that never reaches WRITE_TIME_STEP
+    leaves a 3-record file), then per frame one count record (7 * n_active) and
+    n_active * 7 records."""
 
     def __init__(self, path: str, length_of_area, nbytes: int = 4):
         assert nbytes in (4, 8)
@@ -135,8 +137,7 @@ class OutputWriter:
         self.f = open(path, "wb")
         self.rt = np.dtype("<f4") if nbytes == 4 else np.dtype("<f8")
         self.f.write(np.asarray(length_of_area, dtype=self.rt).tobytes())
-        self.frames = 0
-        self._write_count()
+        self.frames = 0          # record 4 (frames so far) first appears with the first frame (program:336-337)
 
     def _int_record(self, v: int) -> bytes:
         return struct.pack("<i", v) + (b"\0" * (self.nbytes - 4))
@@ -194,6 +195,8 @@ def read_output(path: str, nbytes: int = 4):
 
     area = [rd(ff) for _ in range(3)]
     declared = rd(fi)
+    if declared is None:         # no frame was ever written: the file ends after record 3
+        declared = 0
     frames = []
     while True:
         cnt = rd(fi)

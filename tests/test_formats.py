@@ -222,3 +222,16 @@ def test_cli_tools_round_trip(tmp_path):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "check_output.py"), "-i", out, "--compare", out],
                        capture_output=True, text=True)
     assert r.returncode == 0 and "Number of blocks: 2 (header says 2)" in r.stdout and "max |dx| = 0" in r.stdout
+
+
+@pytest.mark.parametrize("nbytes", [4, 8])
+def test_a_run_without_frames_leaves_three_records(tmp_path, nbytes):
+    """The reference writes record 4 (frames so far) inside write_data only (program:336-337): a run whose
+    MAX_TIME_STEP never reaches WRITE_TIME_STEP leaves length_of_area and nothing else."""
+    from particle_simulation_b200 import formats
+    path = str(tmp_path / "empty.output")
+    with formats.OutputWriter(path, (99.0, 98.0, 97.0), nbytes=nbytes):
+        pass
+    assert os.path.getsize(path) == 3 * nbytes
+    area, declared, frames = formats.read_output(path, nbytes=nbytes)
+    assert area == [99.0, 98.0, 97.0] and declared == 0 and frames == []
