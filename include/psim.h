@@ -80,8 +80,10 @@ typedef enum psim_allpairs_kernel {
   PSIM_ALLPAIRS_DIFFERENCE_FORM = 1, /* the distance test in difference form in the working precision (3 sub, 1 mul,
                                         2 FMA, 1 compare per pair: the literal reading of stoermer:117-121), no
                                         pre-filter; ~5x slower, kept as the plainest statement of the path */
-  PSIM_ALLPAIRS_CUDA_CORE = 5        /* warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in packed
+  PSIM_ALLPAIRS_CUDA_CORE = 5,       /* warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in packed
                                         FP32 (3 FMAs per ordered pair); no tensor cores; 1.5-2x slower than 0 */
+  PSIM_ALLPAIRS_TENSOR_F16 = 7       /* the tensor-core filter as one kind::f16 MMA per tile with FP16 accumulators
+                                        and packed TMEM loads (csrc/psim_allpairs_tc16.cuh) */
 } psim_allpairs_kernel;
 
 typedef enum psim_option {

@@ -1,0 +1,440 @@
+// psim_allpairs_tc16.cuh — the all-pairs force pass with the distance filter as ONE kind::f16 tcgen05.mma per
+// tile, FP16 accumulators in TMEM, packed TMEM loads and a sign test.
+//
+// Why (measured on B200, tools/microbench/tc_f16.cu, profiles/r2_microbench_tc_f16.log).  In the TF32 kernel
+// (psim_allpairs_tc.cuh) a tile of 128 x 128 pair tests costs 128 cycles of tensor pipe (two K = 8 MMAs), and
+// 128 cycles of ALU pipe per SM sub-partition (16 FMNMX3 per 32 values, one every 2 clocks).  With FP16
+// operands the same K = 16 product is ONE instruction at twice the rate (64 cycles per tile); with an FP16
+// accumulator tcgen05.ld .pack::16b delivers two entries per register, so the reduction handles two pairs per
+// lane-operation (64 cycles per tile).  The tensor core forms the 16-term sum at (about) FP32 width and rounds
+// once (measured: error 3.4e-5 on sums whose terms are ~350), so the cancellation |y_i|^2 + |y_j|^2 - 2 y_i.y_j
+// survives; the FP16 rounding of the RESULT only has to keep its sign.
+//
+// Mathematics.  With y = position relative to the box centre, scaled by a power of two S so that |S y|^2 fits
+// FP16, every float is split into two FP16 pieces (11 significant bits each), weights into three:
+//     A row i: x1 x1 x2 | y1 y1 y2 | z1 z1 z2 | 1  1  1  | -C1 -C2 -C3 | 0
+//     B row j: X1 X2 X1 | Y1 Y2 Y1 | Z1 Z2 Z1 | w1 w2 w3 |  1   1   1  | 0        X = -2 S x_j ...
+//     acc(i, j) = w_j - 2 S^2 y_i.y_j - C_i ,   C_i = S^2 r_cut^2 (1 + d) - w_i ,   w = S^2 |y|^2 (1 - k) - a
+// so acc < 0 is the filter's "may be in range".  k = 2^-16 covers the dropped cross terms
+// (<= 3 * 2^-22 (|Sy_i|^2 + |Sy_j|^2)) and the accumulation error with a factor > 5 to spare; a covers the rounding of
+// the coordinates to float (16 u r_cut (|y| + 1), as in the TF32 kernel) plus 2^-13 for FP16 underflow of the
+// smallest pieces and of the result.  Inactive and padding records get a row that can never pass (+60000);
+// a particle so far outside the box that S^2 |y|^2 would overflow FP16 (it left the box and the next rebuild
+// will deactivate it) gets a row that ALWAYS passes (-60000): every pair that passes is decided and evaluated
+// exactly, in the working precision, by the same exact path as before (tc::exact_pair -> pair_force), so the
+// forces are unchanged; the kernel counts the in-range pairs it evaluated for the tests' audit.
+//
+// Organisation (one block of 21 warps per SM, four 128-column FP16 accumulators in TMEM):
+//   * tc16_prepare_kernel writes every particle's B row (32 B) once per force pass in UMMA tile layout;
+//   * the TMA producer streams 32 KB (eight tiles) per bulk copy through a 2-slot ring;
+//   * MMA warp w issues the tiles t = w (mod 4) into accumulator w: one instruction and one commit per tile,
+//     one b_full wait per two tiles (the B slot is handed back by a consumer lane, not by a second commit);
+//   * consumer warps split by tile parity: eight warps (4 lane quadrants x 2 column halves) take the even
+//     tiles, eight the odd ones; a warp reads its 32 rows x 64 columns with one tcgen05.ld.32x32b.x32.pack::16b,
+//     releases the accumulator and ORs the 32 packed registers (16 LOP3): any sign bit set = a candidate.
+//     Software-pipelined over two register sets as in the TF32 kernel; rare hits go to the 16-bit queue.
+//   * j-split and the fixed-order combine: as in psim_allpairs_tc.cuh.
+#pragma once
+
+#include <cuda_fp16.h>
+
+#include "psim_allpairs_tc.cuh"
+
+namespace psim {
+namespace tch {
+
+using tc::M;
+using tc::JSplit;
+constexpr int K = 16;                           // FP16 inner dimension: one MMA
+constexpr int N2 = 128;                         // j records per tile = accumulator columns per buffer
+constexpr int NBUF = 4;                         // TMEM ring: four accumulators of 128 columns
+constexpr int NCTL = NBUF;                      // MMA warps
+constexpr int TILE_BYTES = N2 * K * 2;          // 4 KB
+constexpr int TPS = 8;                          // tiles per ring slot (one 32 KB bulk copy)
+constexpr int NSLOT = 2;
+constexpr int SLOT_BYTES = TPS * TILE_BYTES;
+constexpr int RING_BYTES = NSLOT * SLOT_BYTES;  // 64 KB
+constexpr int CW = 16;                          // consumer warps: (tile parity) x (4 lane quadrants) x (2 column halves)
+constexpr int TW = 32 * (CW + NCTL + 1);
+constexpr int QC = 64, QPHYS = QC + 64;         // queue: logical capacity + one chunk's unbounded first pass (64 columns)
+constexpr int QMAX_TILE = 5;
+constexpr int QSTRIDE = 32 * CW;
+constexpr int SEG = 512;                        // own tiles per consume call: a queue entry holds a 9-bit tile offset
+constexpr int SMEM_BYTES = RING_BYTES + QPHYS * QSTRIDE * 2;   // 64 KB + 128 KB
+constexpr unsigned DENSE = 0x8000u;             // queue entry: [dense:1][own tile - k_begin:9][column:6]
+constexpr float BIG = 60000.0f;                 // fits FP16; larger than any S^2 |y|^2 the scaling admits
+
+// rows x 16 halves (32 B per row): 8-row groups 256 B apart (SBO), the two 16-byte K-chunks of a row 128 B
+// apart (LBO), rows of a group 16 B apart: byte-identical to one K = 8 block of the TF32 layout.
+__device__ __forceinline__ unsigned chunk_off16(int r, int chunk) {   // chunk = k / 8, 0..1
+  return (unsigned)((r >> 3) * 256 + chunk * 128 + (r & 7) * 16);
+}
+
+struct alignas(16) Half8 { __half2 a, b, c, d; };
+
+__device__ __forceinline__ void hsplit2(float x, __half& a, __half& b) {
+  a = __float2half_rn(x); b = __float2half_rn(x - __half2float(a));
+}
+__device__ __forceinline__ void hsplit3(float x, __half& a, __half& b, __half& c) {
+  a = __float2half_rn(x); const float r = x - __half2float(a);
+  b = __float2half_rn(r); c = __float2half_rn(r - __half2float(b));
+}
+
+// The scale: the largest power of two S with (1.4 x half diagonal of the box x S)^2 <= 60000, so that anything
+// inside the box, and well outside it, has a finite FP16 weight.  Computed on the host.
+struct Scale16 { float S, S2; };
+
+// What one particle contributes to the operands.  kind: 0 = normal, 1 = never passes (inactive, padding),
+// 2 = always passes (beyond the FP16 range).
+struct Rec16 { float x, y, z, w; int kind; };
+
+template <class R>
+__device__ __forceinline__ Rec16 filter_record16(const Real4<R>& p, const Consts<R>& c, float rcut, Scale16 sc) {
+  constexpr float u32 = 5.9604645e-8f;
+  Rec16 f;
+  const float fx = (float)r_sub(p.x, r_mul((R)0.5, c.area[0]));
+  const float fy = (float)r_sub(p.y, r_mul((R)0.5, c.area[1]));
+  const float fz = (float)r_sub(p.z, r_mul((R)0.5, c.area[2]));
+  const float n2 = fx * fx + fy * fy + fz * fz;
+  f.x = fx * sc.S; f.y = fy * sc.S; f.z = fz * sc.S;
+  const float n2s = n2 * sc.S2;
+  f.w = n2s * (1.0f - 1.52587890625e-5f) - sc.S2 * 16.0f * u32 * rcut * (sqrtf(n2) + 1.0f) - 1.220703125e-4f;
+  f.kind = 0;
+  if (!(n2s < 0.9f * BIG)) f.kind = 2;         // also catches NaN / inf coordinates
+  if (p.w >= c.huge) f.kind = 1;
+  return f;
+}
+
+// B operand rows of all particles, tile by tile (4 KB per 128 records), in the layout of chunk_off16(); also
+// clears the pair counter of the force kernel that follows.
+template <class R>
+__global__ void __launch_bounds__(256)
+tc16_prepare_kernel(const Real4<R>* __restrict__ pos, unsigned char* __restrict__ bops, int64_t n_pad, Consts<R> c,
+                    Scale16 sc, unsigned long long* __restrict__ pair_count) {
+  const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (j == 0) *pair_count = 0ull;
+  if (j >= n_pad) return;
+  const Rec16 f = filter_record16(pos[j], c, (float)c.r_cut, sc);
+  const __half zero = __float2half_rn(0.f), one = __float2half_rn(1.f);
+  __half x1 = zero, x2 = zero, y1 = zero, y2 = zero, z1 = zero, z2 = zero, w1, w2 = zero, w3 = zero;
+  if (f.kind == 0) {
+    hsplit2(-2.0f * f.x, x1, x2); hsplit2(-2.0f * f.y, y1, y2); hsplit2(-2.0f * f.z, z1, z2);
+    hsplit3(f.w, w1, w2, w3);
+  } else {
+    w1 = __float2half_rn(f.kind == 1 ? BIG : -BIG);
+  }
+  unsigned char* b = bops + (j / N2) * TILE_BYTES;
+  const int r = (int)(j % N2);
+  Half8 c0, c1;
+  c0.a = __halves2half2(x1, x2); c0.b = __halves2half2(x1, y1); c0.c = __halves2half2(y2, y1); c0.d = __halves2half2(z1, z2);
+  c1.a = __halves2half2(z1, w1); c1.b = __halves2half2(w2, w3); c1.c = __halves2half2(one, one); c1.d = __halves2half2(one, zero);
+  *reinterpret_cast<Half8*>(b + chunk_off16(r, 0)) = c0;
+  *reinterpret_cast<Half8*>(b + chunk_off16(r, 1)) = c1;
+}
+
+// A operand row of one i-particle (same record, the other role).
+__device__ __forceinline__ void store_a_row(unsigned char* sA, int row, const Rec16& f, float cut2s) {
+  const __half zero = __float2half_rn(0.f), one = __float2half_rn(1.f);
+  __half x1 = zero, x2 = zero, y1 = zero, y2 = zero, z1 = zero, z2 = zero, o = zero, c1 = zero, c2 = zero, c3 = zero;
+  if (f.kind == 0) {
+    hsplit2(f.x, x1, x2); hsplit2(f.y, y1, y2); hsplit2(f.z, z1, z2);
+    hsplit3(-(cut2s - f.w), c1, c2, c3);
+    o = one;
+  } else {
+    c1 = __float2half_rn(f.kind == 1 ? BIG : -BIG);      // times the 1 in column 12 of every B row
+  }
+  Half8 a0, a1;
+  a0.a = __halves2half2(x1, x1); a0.b = __halves2half2(x2, y1); a0.c = __halves2half2(y1, y2); a0.d = __halves2half2(z1, z1);
+  a1.a = __halves2half2(z2, o); a1.b = __halves2half2(o, o); a1.c = __halves2half2(c1, c2); a1.d = __halves2half2(c3, zero);
+  *reinterpret_cast<Half8*>(sA + chunk_off16(row, 0)) = a0;
+  *reinterpret_cast<Half8*>(sA + chunk_off16(row, 1)) = a1;
+}
+
+#define PSIM_TMEM_LD32_PACK16(r, taddr)                                                                            \
+  asm volatile(                                                                                                    \
+      "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "                                                          \
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                                    \
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"                  \
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),            \
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),      \
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),    \
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])     \
+      : "r"(taddr))
+
+constexpr unsigned SIGNS = 0x80008000u;
+
+// 64 columns of this thread's row as 32 packed registers (low half = even column): OR them (16 LOP3,
+// groups of 9, 9, 9 and 5 registers); a sign bit in the result = some entry is negative = a candidate.
+// The rare hit pushes the negative columns (tile-relative code `tcode`); more than QMAX_TILE of them become
+// ONE dense entry, so a chunk adds at most QMAX_TILE logical entries — the first pass may write up to 64
+// entries past cnt, hence QPHYS.
+__device__ __forceinline__ void queue_chunk16(const unsigned (&r)[32], unsigned tcode, unsigned q, int& cnt) {
+  unsigned mg[4];
+#pragma unroll
+  for (int g = 0; g < 3; ++g)
+    mg[g] = (r[9 * g] | r[9 * g + 1] | r[9 * g + 2]) | (r[9 * g + 3] | r[9 * g + 4] | r[9 * g + 5]) |
+            (r[9 * g + 6] | r[9 * g + 7] | r[9 * g + 8]);
+  mg[3] = (r[27] | r[28] | r[29]) | r[30] | r[31];
+  const unsigned m = (mg[0] | mg[1] | mg[2]) | mg[3];
+  if (m & SIGNS) {
+    const int c0 = cnt;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      if (mg[g] & SIGNS) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+          const int u = 9 * g + k;                 // static after unrolling: r[] must stay in registers
+          if (u < 32) {
+            const unsigned v = r[u < 32 ? u : 0];
+            if (v & 0x00008000u) { tc::q_store(q, cnt, tcode + 2 * u); ++cnt; }
+            if (v & 0x80000000u) { tc::q_store(q, cnt, tcode + 2 * u + 1); ++cnt; }
+          }
+        }
+      }
+    }
+    if (cnt - c0 > QMAX_TILE) {
+      tc::q_store(q, c0, tcode | DENSE);
+      cnt = c0 + 1;
+    }
+  }
+}
+
+template <class R>
+struct FlushCtx16 {
+  const Real4<R>* pos; const Consts<R>* c; int64_t ig;
+  int64_t col0;              // global index of column 0 of this thread's chunk in ITS first tile of the block's j segment
+  R f[3]; unsigned in_range;
+};
+
+// k_begin: the own-tile index that queue codes are relative to; own tile k is tile 2 k + parity of the segment.
+template <class R>
+__device__ __noinline__ void flush_queue16(FlushCtx16<R>* x, unsigned q, int cnt, int k_begin) {
+  if (cnt == 0) return;
+  const Real4<R>* __restrict__ pos = x->pos;
+  const Consts<R>& c = *x->c;
+  const int64_t ig = x->ig;
+  const Real4<R> pi = pos[ig];
+  for (int e = 0; e < cnt; ++e) {
+    const unsigned v = tc::q_load(q, e);
+    const int64_t j0 = (int64_t)(k_begin + (int)((v >> 6) & 511u)) * (2 * N2) + x->col0;
+    if (v & DENSE) {
+      for (int u = 0; u < 64; ++u) tc::exact_pair(pos, c, ig, pi, j0 + u, x->f, &x->in_range);
+    } else {
+      tc::exact_pair(pos, c, ig, pi, j0 + (int64_t)(v & 63u), x->f, &x->in_range);
+    }
+  }
+}
+
+// The consumer tile loop of one warp (a function of its own: its own register allocation, two sets of 32
+// packed registers, loop state in uniform registers — see consume_tiles in psim_allpairs_tc.cuh).  The warp
+// owns the tiles of one parity: own tile k is tile 2 k + p and lives in accumulator p + 2 (k & 1), phase
+// k >> 1.  Groups of four own tiles start at multiples of four, so the phase parities are immediates
+// (0, 0, 1, 1).  lane_base addresses the warp's 64 columns of accumulator p; accumulator p + 2 is 256 columns
+// further.  dbar: shared address of d_full[p]; d_full[p + 2] is 16 bytes further, d_empty[b] 8 * NBUF bytes
+// after d_full[b].  releases_slots: this warp hands the ring slot of its tiles back to the TMA producer: lane 0
+// arrives on b_empty[(t / TPS) % NSLOT] once per own tile after the tile's d_full wait (the MMA that read the
+// B tile is complete then); bempty0 = shared address of b_empty[0].
+// ntk (own tiles): multiple of 4.  Returns (next own tile << 32) | queue length.
+__device__ __noinline__ unsigned long long consume_tiles16(unsigned q, unsigned lane_base, unsigned dbar, unsigned bempty0,
+                                                           int releases_slots, int ntk_v, int k_begin_v) {
+  const int lane = threadIdx.x & 31;
+  const int k_begin = (int)__reduce_max_sync(0xffffffffu, (unsigned)k_begin_v);
+  const int ntk = (int)__reduce_max_sync(0xffffffffu, (unsigned)ntk_v);
+  const bool release_slot = __reduce_max_sync(0xffffffffu, (unsigned)releases_slots) != 0u;   // uniform
+  // own tile k = tile 2 k + p: its ring slot is ((2 k + p) / TPS) % NSLOT = (k / 4) % NSLOT for TPS = 8
+#define PSIM_TC16_ACQUIRE(r, which, par_, kk)                                                     \
+  {                                                                                              \
+    tc::mbar_wait_warp(dbar + 16u * (which), (par_));                                            \
+    asm volatile("tcgen05.fence::after_thread_sync;");                                           \
+    PSIM_TMEM_LD32_PACK16(r, lane_base + (unsigned)((which) * 2 * N2));                          \
+    if (release_slot && lane == 0) tc::mbar_arrive(bempty0 + 8u * (unsigned)(((kk) >> 2) % NSLOT)); \
+  }
+#define PSIM_TC16_RELEASE(which)                                                                 \
+  {                                                                                              \
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");                                 \
+    asm volatile("tcgen05.fence::before_thread_sync;");                                          \
+    __syncwarp();                                                                                \
+    if (lane == 0) tc::mbar_arrive(dbar + 8u * NBUF + 16u * (which));                            \
+  }
+  unsigned rA[32], rB[32];
+  int cnt = 0, k0 = k_begin;
+  PSIM_TC16_ACQUIRE(rA, 0, 0u, k0)
+  for (;;) {
+    const unsigned tc0 = (unsigned)(k0 - k_begin) << 6;
+    const bool more = (k0 + 4 < ntk) && (k0 + 4 - k_begin < SEG) &&
+                      !__any_sync(0xffffffffu, cnt > QC - 8 * QMAX_TILE);
+    PSIM_TC16_RELEASE(0) PSIM_TC16_ACQUIRE(rB, 1, 0u, k0 + 1)
+    queue_chunk16(rA, tc0, q, cnt);
+    PSIM_TC16_RELEASE(1) PSIM_TC16_ACQUIRE(rA, 0, 1u, k0 + 2)
+    queue_chunk16(rB, tc0 + 64u, q, cnt);
+    PSIM_TC16_RELEASE(0) PSIM_TC16_ACQUIRE(rB, 1, 1u, k0 + 3)
+    queue_chunk16(rA, tc0 + 128u, q, cnt);
+    PSIM_TC16_RELEASE(1)
+    if (more) PSIM_TC16_ACQUIRE(rA, 0, 0u, k0 + 4)
+    queue_chunk16(rB, tc0 + 192u, q, cnt);
+    k0 += 4;
+    if (!more) break;
+  }
+#undef PSIM_TC16_ACQUIRE
+#undef PSIM_TC16_RELEASE
+  return ((unsigned long long)(unsigned)k0 << 32) | (unsigned)cnt;
+}
+
+template <class R, int MODE>
+__global__ void __launch_bounds__(TW, 1)
+allpairs_tc16_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, unsigned long long* __restrict__ pair_count,
+                     const JSplit<R> js, const Scale16 sc) {
+  extern __shared__ __align__(1024) unsigned char sB[];          // ring of B tiles, then the candidate queues
+  __shared__ __align__(128) unsigned char sA[M * K * 2];          // 4 KB
+  __shared__ __align__(8) unsigned long long b_full[NSLOT], b_empty[NSLOT], d_bar[2 * NBUF];   // d_bar: full[0..3], empty[0..3]
+  unsigned long long* const d_full = d_bar;
+  unsigned long long* const d_empty = d_bar + NBUF;
+  __shared__ unsigned tmem_base_s;
+  __shared__ int last_s;
+  __shared__ R fpart[4][3][M];
+
+  const Consts<R>& c = a.c;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool consumer = warp < CW;
+  const int row = (warp & 3) * 32 + lane;          // accumulator row = TMEM lane (consumers)
+  const int grp = (warp >> 2) & 3;                 // consumers: tile parity (grp >> 1) and column half (grp & 1)
+  const int par = grp >> 1, half64 = grp & 1;
+  const int S = js.S;
+  const int ib = (int)blockIdx.x / S, seg = (int)blockIdx.x - ib * S;
+  const int64_t ig = a.i_lo + (int64_t)ib * M + row;
+  const float rcut = (float)c.r_cut;
+  const float cut2s = (float)c.cut2_pad * (1.0f + 1.0e-6f) * sc.S2;
+  // this block's j segment, in tiles (multiples of 8: whole ring slots, whole phase pairs)
+  const int nt8 = (int)(a.n_pad / (8 * N2));
+  const int t_lo = 8 * ((seg * nt8) / S), t_hi = 8 * (((seg + 1) * nt8) / S);
+  const int nt = t_hi - t_lo;
+
+  // --- A tile: this block's i-particles ---
+  if (consumer && grp == 0) {
+    Rec16 f; f.x = f.y = f.z = f.w = 0.f; f.kind = 1;
+    if (ig < a.i_hi) f = filter_record16(a.pos_cur[ig], c, rcut, sc);
+    store_a_row(sA, row, f, cut2s);
+  }
+  if (tid == 0) {
+    for (int s = 0; s < NSLOT; ++s) { tc::mbar_init(tc::smem_u32(&b_full[s]), 1); tc::mbar_init(tc::smem_u32(&b_empty[s]), TPS); }
+    for (int b = 0; b < NBUF; ++b) { tc::mbar_init(tc::smem_u32(&d_full[b]), 1); tc::mbar_init(tc::smem_u32(&d_empty[b]), CW / 2); }
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  if (warp == CW) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(tc::smem_u32(&tmem_base_s)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // A tile: generic-proxy writes -> tensor core
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  const unsigned tm = tmem_base_s;
+
+  FlushCtx16<R> fx;
+  fx.pos = a.pos_cur; fx.c = &c; fx.ig = ig; fx.col0 = (int64_t)(t_lo + par) * N2 + half64 * 64;
+  fx.f[0] = fx.f[1] = fx.f[2] = (R)0; fx.in_range = 0;
+  if (warp == CW + NCTL) {
+    if (lane == 0) {
+      // ===== TMA producer: one 32 KB bulk copy per eight tiles (this GPU's memory), as far ahead as the ring allows =====
+      const int nq = nt / TPS;
+      const unsigned bfull0 = tc::smem_u32(&b_full[0]), bempty0 = tc::smem_u32(&b_empty[0]), sB0 = tc::smem_u32(sB);
+      const unsigned char* src = bops + (size_t)t_lo * TILE_BYTES;
+      for (int Q = 0; Q < nq; ++Q) {
+        const int s = Q % NSLOT;
+        tc::mbar_wait(bempty0 + 8u * s, (unsigned)(((Q / NSLOT) & 1) ^ 1));   // all eight tiles of the slot multiplied (fresh: passes)
+        tc::mbar_expect_tx(bfull0 + 8u * s, SLOT_BYTES);
+        tc::bulk_copy_g2s(sB0 + (unsigned)(s * SLOT_BYTES), src + (size_t)Q * SLOT_BYTES, SLOT_BYTES, bfull0 + 8u * s);
+      }
+    }
+  } else if (warp >= CW) {
+    if (lane == 0) {
+      // ===== MMA warp w: issues the tiles t = w, w + 4, ... into accumulator w: one instruction, one commit =====
+      const int w = warp - CW;
+      const int ntw = nt / NCTL;                   // nt is a multiple of 8
+      // D = F16 (c_format 0), A and B = F16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+      const unsigned idesc = ((unsigned)(N2 >> 3) << 17) | ((unsigned)(M >> 4) << 24);
+      const unsigned long long da = tc::make_desc(tc::smem_u32(sA));
+      const unsigned acc = tm + (unsigned)(w * N2);
+      const unsigned dfull = tc::smem_u32(&d_full[w]), dempty = tc::smem_u32(&d_empty[w]);
+      const unsigned bfull0 = tc::smem_u32(&b_full[0]), sB0 = tc::smem_u32(sB);
+      for (int k = 0; k < ntw; ++k) {
+        const int Q = k >> 1, s = Q % NSLOT;       // tile t = w + 4 k sits in ring fill Q = t / 8, at position w + 4 (k & 1)
+        if ((k & 1) == 0) tc::mbar_wait(bfull0 + 8u * s, (unsigned)((Q / NSLOT) & 1));      // the slot's eight tiles landed
+        tc::mbar_wait(dempty, (unsigned)((k & 1) ^ 1));                                     // accumulator drained
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const unsigned long long db = tc::make_desc(sB0 + (unsigned)(s * SLOT_BYTES + (w + 4 * (k & 1)) * TILE_BYTES));
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
+            :: "r"(acc), "l"(da), "l"(db), "r"(idesc), "r"(0u), "r"(0u), "r"(0u), "r"(0u), "r"(0u));
+        tc::umma_commit(dfull);
+      }
+    }
+  } else {
+    // ===== consumers =====
+    const unsigned q = tc::smem_u32(sB + RING_BYTES) + 2u * (unsigned)tid;
+    const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(par * N2 + half64 * 64);
+    const unsigned dbar = tc::smem_u32(&d_bar[par]);
+    const unsigned bempty0 = tc::smem_u32(&b_empty[0]);
+    const int releases = ((warp & 3) == 0 && half64 == 0) ? 1 : 0;     // one warp per tile parity hands the ring slots back
+    const int ntk = nt / 2;
+    int k = 0;
+    while (k < ntk) {
+      const unsigned long long r = consume_tiles16(q, lane_base, dbar, bempty0, releases, ntk, k);
+      flush_queue16<R>(&fx, q, (int)(unsigned)r, k);
+      k = (int)(r >> 32);
+    }
+    unsigned in_range = fx.in_range;
+    for (int off = 16; off > 0; off >>= 1) in_range += __shfl_xor_sync(0xffffffffu, in_range, off);
+    if (lane == 0 && in_range) atomicAdd(pair_count, (unsigned long long)in_range);
+  }
+
+  // --- the four threads of a row meet (fixed order) ---
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  R* const f = fx.f;
+  if (consumer && grp > 0) { fpart[grp][0][row] = f[0]; fpart[grp][1][row] = f[1]; fpart[grp][2][row] = f[2]; }
+  __syncthreads();
+  const bool owner = consumer && grp == 0;
+  if (owner) {
+#pragma unroll
+    for (int g = 1; g < 4; ++g) {
+      f[0] = r_add(f[0], fpart[g][0][row]); f[1] = r_add(f[1], fpart[g][1][row]); f[2] = r_add(f[2], fpart[g][2][row]);
+    }
+  }
+  if (warp == CW) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tm));
+  }
+  // --- the j segments of an i-block meet in global scratch (psim_allpairs_tc.cuh) ---
+  bool finish = true;
+  if (S > 1) {
+    if (owner) {
+      R* p = js.part + (size_t)blockIdx.x * 3 * M;
+      p[row] = f[0]; p[M + row] = f[1]; p[2 * M + row] = f[2];
+      __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned prev = atomicAdd(&js.arrived[ib], 1u);
+      last_s = (prev == (unsigned)S - 1u) ? 1 : 0;
+      if (last_s) js.arrived[ib] = 0u;
+    }
+    __syncthreads();
+    finish = last_s != 0;
+    if (finish && owner) {
+      __threadfence();
+      const volatile R* p = js.part + (size_t)ib * S * 3 * M;
+      f[0] = p[row]; f[1] = p[M + row]; f[2] = p[2 * M + row];
+      for (int s = 1; s < S; ++s) {
+        const volatile R* ps = p + (size_t)s * 3 * M;
+        f[0] = r_add(f[0], ps[row]); f[1] = r_add(f[1], ps[M + row]); f[2] = r_add(f[2], ps[2 * M + row]);
+      }
+    }
+  }
+  R first = (R)0, second = (R)0;
+  if (finish && owner && ig < a.i_hi) step_epilogue<R, MODE>(a, ig, f[0], f[1], f[2], first, second);
+  if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, TW>(first, second, a.top2_part, a.ticket, a.rank_pair);
+}
+
+}  // namespace tch
+}  // namespace psim

@@ -23,6 +23,7 @@
 #include "psim_allpairs.cuh"
 #include "psim_allpairs2.cuh"
 #include "psim_allpairs_tc.cuh"
+#include "psim_allpairs_tc16.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -190,7 +191,8 @@ class SimT final : public psim_sim {
   unsigned* tc_arrived = nullptr;       // ... j-split: arrival counter per i-block (zero between launches)
   int64_t tc_part_cap = 0;
   double* red_scratch = nullptr;        // 8 doubles: reductions of count_pairs / energy (no allocation per call)
-  bool attr_tc[3] = {false, false, false};
+  bool attr_tc[3] = {false, false, false}, attr_tc16[3] = {false, false, false};
+  tch::Scale16 scale16 = {1.0f, 1.0f};
   CellPath<R> cells;
   // options
   int algo = PSIM_FORCE_ALL_PAIRS;
@@ -252,6 +254,11 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
     if (const char* e = std::getenv("PSIM_RI")) { const int v = std::atoi(e); if (v >= 6 && v <= 8) ri_sel = v; }   // tuning knobs
     if (const char* e = std::getenv("PSIM_WARPS")) { const int v = std::atoi(e); if (v == 4 || v == 8 || v == 16) warps_forced = v; }
+    if (const char* e = std::getenv("PSIM_ALLPAIRS_KERNEL")) {   // testing: run everything through one kernel
+      const int v = std::atoi(e);
+      if (v == PSIM_ALLPAIRS_TENSOR || v == PSIM_ALLPAIRS_DIFFERENCE_FORM || v == PSIM_ALLPAIRS_CUDA_CORE || v == PSIM_ALLPAIRS_TENSOR_F16)
+        variant = v;
+    }
     if (const char* e = std::getenv("PSIM_JSPLIT")) { const int v = std::atoi(e); if (v >= 1 && v <= tc::MAX_JSPLIT) jsplit_forced = v; }
     if (const char* e = std::getenv("PSIM_CLUSTER")) {
       const int v = std::atoi(e);
@@ -259,6 +266,13 @@ class SimT final : public psim_sim {
     }
     c = derive_consts<R>(p);
     mass = p.mass;
+    {   // FP16 operand scale of the tensor-core filter: largest power of two with (1.4 x half diagonal x S)^2 <= 60000
+      double d2 = 0;
+      for (int d = 0; d < 3; ++d) d2 += p.length_of_area[d] * p.length_of_area[d];
+      const double lim = std::sqrt((double)tch::BIG) / (1.4 * 0.5 * std::sqrt(d2));
+      const float S = (float)std::ldexp(1.0, (int)std::floor(std::log2(lim)));
+      scale16.S = S; scale16.S2 = S * S;
+    }
     if (!(c.min_cell >= c.r_cut)) {
       // the reference's lists would then drop pairs inside the cutoff
       // (module_particle_management.f08:384 keeps r <= min_length_of_cell only)
@@ -447,6 +461,36 @@ class SimT final : public psim_sim {
         attr_tc[MODE] = true;
       }
       tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs, js);
+      return PSIM_OK;
+    }
+    if (variant == PSIM_ALLPAIRS_TENSOR_F16) {   // one kind::f16 MMA per tile, FP16 accumulators, packed loads
+      const int64_t iblocks = blocks(i_hi - i_lo, tc::M);
+      tc::JSplit<R> js;
+      js.S = pick_jsplit(iblocks); js.part = nullptr; js.arrived = nullptr;
+      *grid_out = iblocks * js.S;
+      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
+      if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
+      if (js.S > 1) {
+        if (tc_part_cap < *grid_out) {
+          cudaFree(tc_part); tc_part = nullptr;
+          PSIM_CK(cudaMalloc(&tc_part, sizeof(R) * 3 * tc::M * (size_t)*grid_out));
+          tc_part_cap = *grid_out;
+        }
+        if (!tc_arrived) {
+          const size_t cnt = (size_t)blocks(shard, tc::M) + 1;
+          PSIM_CK(cudaMalloc(&tc_arrived, sizeof(unsigned) * cnt));
+          PSIM_CK(cudaMemsetAsync(tc_arrived, 0, sizeof(unsigned) * cnt, stream));
+        }
+        js.part = tc_part; js.arrived = tc_arrived;
+      }
+      tch::tc16_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, scale16, tc_pairs);
+      ++launches;
+      constexpr int kSmem = tch::SMEM_BYTES;
+      if (!attr_tc16[MODE]) {
+        PSIM_CK(cudaFuncSetAttribute(tch::allpairs_tc16_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_tc16[MODE] = true;
+      }
+      tch::allpairs_tc16_kernel<R, MODE><<<(unsigned)*grid_out, tch::TW, kSmem, stream>>>(a, tc_bops, tc_pairs, js, scale16);
       return PSIM_OK;
     }
     if (variant == PSIM_ALLPAIRS_DIFFERENCE_FORM) {   // the literal reading of stoermer:117-121 in the working precision
@@ -659,7 +703,7 @@ class SimT final : public psim_sim {
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
     unsigned long long fp = 0;
-    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && variant == PSIM_ALLPAIRS_TENSOR && tc_pairs;
+    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && (variant == PSIM_ALLPAIRS_TENSOR || variant == PSIM_ALLPAIRS_TENSOR_F16) && tc_pairs;
     if (tracked) PSIM_CK(cudaMemcpyAsync(&fp, tc_pairs, sizeof fp, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     out->filter_pairs = tracked ? (int64_t)fp : -1;
@@ -691,7 +735,8 @@ class SimT final : public psim_sim {
       case PSIM_OPT_ALLPAIRS_KERNEL:
         // 3 and 6 selected the round-1 tensor-core kernels: both are today's default
         if (value == 3 || value == 6) value = PSIM_ALLPAIRS_TENSOR;
-        if (value != PSIM_ALLPAIRS_TENSOR && value != PSIM_ALLPAIRS_DIFFERENCE_FORM && value != PSIM_ALLPAIRS_CUDA_CORE)
+        if (value != PSIM_ALLPAIRS_TENSOR && value != PSIM_ALLPAIRS_DIFFERENCE_FORM && value != PSIM_ALLPAIRS_CUDA_CORE &&
+            value != PSIM_ALLPAIRS_TENSOR_F16)
           return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;
