@@ -239,6 +239,10 @@ psim_status psim_energy(psim_sim* sim, double* kinetic, double* potential,
  * (dr_max_first + dr_max_second > dr_max_tolerable) as 0/1 to the device int
  * *rebuild_flag_dev.  Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the
  * default stream); the CUDA device that is current at the call is used.
+ * The n particles of a call form ONE trigger slice, whatever
+ * params->nb_of_threads says: a host that wants the reference's per-thread
+ * verdicts (NB_OF_THREADS > 1, program_...:71,86,92) calls it once per slice on
+ * the sub-arrays, one call after the other, and ORs the flags.
  *
  * Its reduction scratch is a fixed array inside the library image, not an
  * allocation: PSIM_STATIC_SCRATCH_BYTES per GPU that loads the library, held

@@ -89,6 +89,26 @@ def test_simu_cli_writer_thread_file_is_byte_identical_to_sync_io(psim, tmp_path
     assert outs[0] == outs[1] and len(outs[0]) > 4 * 4
 
 
+@pytest.mark.parametrize("precision", [4, 8])
+def test_simu_cli_run_without_frames_leaves_three_records(psim, tmp_path, precision):
+    """MAX_TIME_STEP < WRITE_TIME_STEP: write_data never runs, so record 4 is never written
+    (program:336-337) and the file is length_of_area alone."""
+    import re
+    from particle_simulation_b200 import build, formats
+    text = open(os.path.join(GOLDEN, "two_cubes.nml")).read()
+    text = re.sub(r"(?i)(WRITE_TIME_STEP\s*=\s*)\d+", r"\g<1>50", text)
+    text = re.sub(r"(?i)(MAX_TIME_STEP\s*=\s*)\d+", r"\g<1>7", text)
+    nml = tmp_path / "short.nml"
+    nml.write_text(text)
+    out = str(tmp_path / "short.output")
+    r = subprocess.run([build.SIMU, str(nml), os.path.join(GOLDEN, "two_cubes.dat"), out, "--precision", str(precision)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert os.path.getsize(out) == 3 * precision
+    area, declared, frames = formats.read_output(out, nbytes=precision)
+    assert declared == 0 and frames == []
+
+
 def test_frame_ring_matches_synchronous_frames(psim):
     ids, pos, vel = two_cubes()
     sim = psim.Simulation(psim.make_params(), ids, pos, vel, 4)
