@@ -16,7 +16,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 OUT = os.path.join(PKG, "_build")
-LIB = os.path.join(OUT, "libpsim_b200.so")
+LIB = os.environ.get("PSIM_LIBRARY") or os.path.join(OUT, "libpsim_b200.so")   # PSIM_LIBRARY: a differently built library (profiling)
 SIMU = os.path.join(OUT, "simu_b200")
 
 NVCC_FLAGS = [

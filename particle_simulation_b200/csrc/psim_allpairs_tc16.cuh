@@ -163,6 +163,16 @@ __device__ __forceinline__ void store_a_row(unsigned char* sA, int row, const Re
 
 constexpr unsigned SIGNS = 0x80008000u;
 
+// -DPSIM_TC_PROF: clock64 timeline of block 0 (tiles 0..511), printed at the end of the kernel.
+// events: 0..3 per MMA warp: [4 w + 0] b_full/d_empty seen, [4 w + 1] issued + committed;
+//         16 + 3 * consumer warp + {0: d_full seen, 1: load complete, 2: accumulator released}
+#ifdef PSIM_TC_PROF
+__device__ long long g_trace16[16 + 3 * CW][512];
+#define TR16(ev, tile) { if (blockIdx.x == 0 && (tile) < 512) g_trace16[ev][tile] = clock64(); }
+#else
+#define TR16(ev, tile) {}
+#endif
+
 // 64 columns of this thread's row as 32 packed registers (low half = even column): OR them (16 LOP3,
 // groups of 9, 9, 9 and 5 registers); a sign bit in the result = some entry is negative = a candidate.
 // The rare hit pushes the negative columns (tile-relative code `tcode`); more than QMAX_TILE of them become
@@ -245,16 +255,19 @@ __device__ __noinline__ unsigned long long consume_tiles16(unsigned q, unsigned 
 #define PSIM_TC16_ACQUIRE(r, which, par_, kk)                                                     \
   {                                                                                              \
     tc::mbar_wait_warp(dbar + 16u * (which), (par_));                                            \
+    if (lane == 0) TR16(16 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
     asm volatile("tcgen05.fence::after_thread_sync;");                                           \
     PSIM_TMEM_LD32_PACK16(r, lane_base + (unsigned)((which) * 2 * N2));                          \
     if (release_slot && lane == 0) tc::mbar_arrive(bempty0 + 8u * (unsigned)(((kk) >> 2) % NSLOT)); \
   }
-#define PSIM_TC16_RELEASE(which)                                                                 \
+#define PSIM_TC16_RELEASE(which, kk)                                                             \
   {                                                                                              \
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");                                 \
+    if (lane == 0) TR16(17 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
     asm volatile("tcgen05.fence::before_thread_sync;");                                          \
     __syncwarp();                                                                                \
     if (lane == 0) tc::mbar_arrive(dbar + 8u * NBUF + 16u * (which));                            \
+    if (lane == 0) TR16(18 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
   }
   unsigned rA[32], rB[32];
   int cnt = 0, k0 = k_begin;
@@ -263,13 +276,13 @@ __device__ __noinline__ unsigned long long consume_tiles16(unsigned q, unsigned 
     const unsigned tc0 = (unsigned)(k0 - k_begin) << 6;
     const bool more = (k0 + 4 < ntk) && (k0 + 4 - k_begin < SEG) &&
                       !__any_sync(0xffffffffu, cnt > QC - 8 * QMAX_TILE);
-    PSIM_TC16_RELEASE(0) PSIM_TC16_ACQUIRE(rB, 1, 0u, k0 + 1)
+    PSIM_TC16_RELEASE(0, k0) PSIM_TC16_ACQUIRE(rB, 1, 0u, k0 + 1)
     queue_chunk16(rA, tc0, q, cnt);
-    PSIM_TC16_RELEASE(1) PSIM_TC16_ACQUIRE(rA, 0, 1u, k0 + 2)
+    PSIM_TC16_RELEASE(1, k0 + 1) PSIM_TC16_ACQUIRE(rA, 0, 1u, k0 + 2)
     queue_chunk16(rB, tc0 + 64u, q, cnt);
-    PSIM_TC16_RELEASE(0) PSIM_TC16_ACQUIRE(rB, 1, 1u, k0 + 3)
+    PSIM_TC16_RELEASE(0, k0 + 2) PSIM_TC16_ACQUIRE(rB, 1, 1u, k0 + 3)
     queue_chunk16(rA, tc0 + 128u, q, cnt);
-    PSIM_TC16_RELEASE(1)
+    PSIM_TC16_RELEASE(1, k0 + 3)
     if (more) PSIM_TC16_ACQUIRE(rA, 0, 0u, k0 + 4)
     queue_chunk16(rB, tc0 + 192u, q, cnt);
     k0 += 4;
@@ -360,7 +373,9 @@ allpairs_tc16_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
       for (int k = 0; k < ntw; ++k) {
         const int Q = k >> 1, s = Q % NSLOT;       // tile t = w + 4 k sits in ring fill Q = t / 8, at position w + 4 (k & 1)
         if ((k & 1) == 0) tc::mbar_wait(bfull0 + 8u * s, (unsigned)((Q / NSLOT) & 1));      // the slot's eight tiles landed
+        TR16(4 * w + 2, w + 4 * k)
         tc::mbar_wait(dempty, (unsigned)((k & 1) ^ 1));                                     // accumulator drained
+        TR16(4 * w + 0, w + 4 * k)
         asm volatile("tcgen05.fence::after_thread_sync;");
         const unsigned long long db = tc::make_desc(sB0 + (unsigned)(s * SLOT_BYTES + (w + 4 * (k & 1)) * TILE_BYTES));
         asm volatile(
@@ -368,6 +383,7 @@ allpairs_tc16_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
             :: "r"(acc), "l"(da), "l"(db), "r"(idesc), "r"(0u), "r"(0u), "r"(0u), "r"(0u), "r"(0u));
         tc::umma_commit(dfull);
+        TR16(4 * w + 1, w + 4 * k)
       }
     }
   } else {
@@ -431,6 +447,19 @@ allpairs_tc16_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops
       }
     }
   }
+#ifdef PSIM_TC_PROF
+  __syncthreads();
+  if (blockIdx.x == 0 && tid == 0) {
+    const long long z = g_trace16[2][256];
+    for (int t = 256; t < 268; ++t) {
+      const int w = t & 3, p = t & 1;
+      printf("TR t=%d mma: b_full %lld d_empty %lld committed %lld |", t, g_trace16[4 * w + 2][t] - z, g_trace16[4 * w][t] - z, g_trace16[4 * w + 1][t] - z);
+      for (int cw = 8 * p; cw < 8 * p + 8; ++cw)
+        printf(" w%d: %lld %lld %lld", cw, g_trace16[16 + 3 * cw][t] - z, g_trace16[17 + 3 * cw][t] - z, g_trace16[18 + 3 * cw][t] - z);
+      printf("\n");
+    }
+  }
+#endif
   R first = (R)0, second = (R)0;
   if (finish && owner && ig < a.i_hi) step_epilogue<R, MODE>(a, ig, f[0], f[1], f[2], first, second);
   if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, TW>(first, second, a.top2_part, a.ticket, a.rank_pair);
