@@ -71,8 +71,6 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--exact-diff", action="store_true", help="difference-form distance test (no pre-filter)")
-    ap.add_argument("--tensor-f16", action="store_true", help="all-pairs with the FP16-operand / FP16-accumulator "
-                    "tensor-core kernel (PSIM_ALLPAIRS_TENSOR_F16)")
     ap.add_argument("--cuda-core", "--ffma2", dest="cuda_core", action="store_true",
                     help="all-pairs on the CUDA cores only (packed-FP32 filter kernel) instead of the default "
                          "tensor-core filter kernel")
@@ -300,7 +298,7 @@ class Ctx:
 
     def simulation(self, params, ids, pos, vel, prec, kernel):
         """A handle on this rank's GPU with the force path `kernel` selected:
-        'allpairs' (tensor-core default), 'allpairs_f16', 'cuda_core', 'exact_diff' or 'cells'."""
+        'allpairs' (tensor-core default), 'cuda_core', 'exact_diff' or 'cells'."""
         import particle_simulation_b200 as P
         from particle_simulation_b200 import native
         sim = P.Simulation(params, ids, pos, vel, prec, device=self.local_rank, rank=self.rank, world=self.world,
@@ -311,8 +309,6 @@ class Ctx:
             sim.set_option(P.OPT_ALLPAIRS_KERNEL, P.ALLPAIRS_CUDA_CORE)
         elif kernel == "exact_diff":
             sim.set_option(P.OPT_ALLPAIRS_KERNEL, P.ALLPAIRS_DIFFERENCE_FORM)
-        elif kernel == "allpairs_f16":
-            sim.set_option(P.OPT_ALLPAIRS_KERNEL, P.ALLPAIRS_TENSOR_F16)
         if kernel != "allpairs":
             sim.set_positions(pos.astype(native.rt(prec)))     # initial forces through the selected path
         return sim
@@ -355,7 +351,7 @@ def parity_check(ctx, params, ids, pos, vel, prec, kernel, ans):
     }
 
 
-def tensor_peak(ctx, f16=False):
+def tensor_peak(ctx, f16=True):
     """Dense tcgen05.mma rate of this GPU for the kind the kernel issues (kind::tf32, or kind::f16), measured
     live by the library (one issuing thread per SM, M128 N256 back to back); falls back to MEASURED_PEAKS.json's
     cuBLAS bf16 burst figure (/ 2 for kind::tf32)."""
@@ -442,8 +438,8 @@ def measure_path(ctx, params, ids, pos, vel, prec, kernel, steps, warmup, sample
         "traffic": recorded_traffic(kernel, n, prec, ctx.world),
         "traffic_note": "dram bytes per launch from the ncu capture of this configuration under profiles/ (null: none on file)",
     }
-    if kernel in ("allpairs", "allpairs_f16"):
-        f16 = kernel == "allpairs_f16"
+    if kernel == "allpairs":
+        f16 = True                          # the kernel issues kind::f16 MMAs
         peak, peak_src = tensor_peak(ctx, f16)
         n_pad_cols = ((n + 1024 * ctx.world - 1) // (1024 * ctx.world)) * 1024 * ctx.world
         tensor_flops = 32.0 * n_own * n_pad_cols          # 2 * K flops per accumulator entry, K = 16
@@ -451,7 +447,7 @@ def measure_path(ctx, params, ids, pos, vel, prec, kernel, steps, warmup, sample
         roofline = dict(common, **{
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak if peak else None, "peak_source": peak_src,
-            "kernel": "tch::allpairs_tc16_kernel" if f16 else "tc::allpairs_tc_kernel", "flops_per_launch": tensor_flops,
+            "kernel": "tc::allpairs_tc_kernel", "flops_per_launch": tensor_flops,
             "flops_accounting": "tensor pipe: 2*K = 32 flops per ordered pair tested (split-%s Gram matrix, K = 16, "
                                 "of which %d columns carry data); SURVEY.md 8(d)'s CUDA-core "
                                 "accounting (8 per pair tested + 15 per pair in range) is reported as survey_tflops"
@@ -521,8 +517,7 @@ def main():
     prec, n = args.precision, args.n
     ids, pos, vel, area = workload(n)
     params = P.make_params(length_of_area=area)
-    kernel = ("cells" if args.algo == "cells" else "exact_diff" if args.exact_diff else "cuda_core" if args.cuda_core
-              else "allpairs_f16" if args.tensor_f16 else "allpairs")
+    kernel = "cells" if args.algo == "cells" else "exact_diff" if args.exact_diff else "cuda_core" if args.cuda_core else "allpairs"
 
     main_m = measure_path(ctx, params, ids, pos, vel, prec, kernel, args.steps, args.warmup, sample_clocks=True)
 
@@ -555,7 +550,7 @@ def main():
     if "parity" in main_m:
         line["parity"] = main_m["parity"]
 
-    if kernel in ("allpairs", "allpairs_f16") and not args.no_cells:
+    if kernel == "allpairs" and not args.no_cells:
         # The same job through the cell-binned path: what a user who wants timesteps/s
         # selects.  Same measurement: value, roofline, e2e, parity.
         csteps = max(args.steps, 200)
@@ -595,7 +590,7 @@ def main():
                 failed.append("cells+drift")
         line["cell_binned"] = cm
 
-    if kernel in ("allpairs", "allpairs_f16") and world >= 8 and n != N_STRONG:
+    if kernel == "allpairs" and world >= 8 and n != N_STRONG:
         # the fixed-size strong-scaling line of configs[3] on this many GPUs, beside the configs[4] headline
         ids_s, pos_s, vel_s, area_s = workload(N_STRONG)
         params_s = P.make_params(length_of_area=area_s)

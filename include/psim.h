@@ -74,16 +74,15 @@ typedef enum psim_force_algo {
  * (one rounding per operation in the order of stoermer:117-128); results differ by summation order only. */
 typedef enum psim_allpairs_kernel {
   PSIM_ALLPAIRS_TENSOR = 0,          /* default: the distance filter of every ordered pair runs on the tensor cores
-                                        (tcgen05.mma kind::tf32 on split operands, TMEM accumulators, TMA-fed), the
-                                        exact pair arithmetic on the CUDA cores for the few pairs that pass.  The
-                                        round-1 values 3 and 6 are accepted as aliases. */
+                                        (one tcgen05.mma kind::f16 per 128 x 128 pairs on split FP16 operands, FP16
+                                        accumulators in TMEM, TMA-fed, packed TMEM loads and a sign test), the exact
+                                        pair arithmetic on the CUDA cores for the few pairs that pass.  The round-1
+                                        values 3 and 6 are accepted as aliases. */
   PSIM_ALLPAIRS_DIFFERENCE_FORM = 1, /* the distance test in difference form in the working precision (3 sub, 1 mul,
                                         2 FMA, 1 compare per pair: the literal reading of stoermer:117-121), no
                                         pre-filter; ~5x slower, kept as the plainest statement of the path */
-  PSIM_ALLPAIRS_CUDA_CORE = 5,       /* warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in packed
-                                        FP32 (3 FMAs per ordered pair); no tensor cores; 1.5-2x slower than 0 */
-  PSIM_ALLPAIRS_TENSOR_F16 = 7       /* the tensor-core filter as one kind::f16 MMA per tile with FP16 accumulators
-                                        and packed TMEM loads (csrc/psim_allpairs_tc16.cuh) */
+  PSIM_ALLPAIRS_CUDA_CORE = 5        /* warp-autonomous CUDA-core kernel with the norm-expansion pre-filter in packed
+                                        FP32 (3 FMAs per ordered pair); no tensor cores; ~3x slower than 0 */
 } psim_allpairs_kernel;
 
 typedef enum psim_option {
@@ -272,8 +271,8 @@ psim_status psim_measure_fma_peak(int precision, int device, double* tflops,
 
 /* Dense tcgen05.mma rate of this GPU in TFLOP/s: one issuing thread per SM on all
  * SMs, M128 N256 instructions back to back into two TMEM accumulators.  kind 0 =
- * kind::tf32 (K = 8 per instruction, what the default all-pairs kernel issues),
- * kind 1 = kind::f16 (K = 16).  The roofline denominator of the tensor-core
+ * kind::tf32 (K = 8 per instruction), kind 1 = kind::f16 (K = 16, what the
+ * default all-pairs kernel issues).  The roofline denominator of the tensor-core
  * kernel (MEASURED_PEAKS.json has a cuBLAS bf16 figure only). */
 psim_status psim_measure_tensor_peak(int kind, int device, double* tflops, double* sm_mhz);
 

@@ -8,7 +8,7 @@ library behind include/psim.h (csrc/); this package is the thin Python host.
 """
 from . import formats, generate, native, sharding  # noqa: F401
 from .native import (  # noqa: F401
-    ALLPAIRS_CUDA_CORE, ALLPAIRS_DIFFERENCE_FORM, ALLPAIRS_TENSOR, ALLPAIRS_TENSOR_F16, FORCE_ALL_PAIRS, FORCE_CELL_BINNED,
+    ALLPAIRS_CUDA_CORE, ALLPAIRS_DIFFERENCE_FORM, ALLPAIRS_TENSOR, FORCE_ALL_PAIRS, FORCE_CELL_BINNED,
     OPT_ALLPAIRS_KERNEL, OPT_EXACT_DIFF_FILTER, OPT_FORCE_ALGO, OPT_FUSED_STEP, OPT_KERNEL_TIMING, Params, PsimError, Simulation, compute_forces, make_params,
 )
 

@@ -1,114 +1,83 @@
-// psim_allpairs_tc.cuh — the default all-pairs force pass: the distance filter of every ordered pair on the
-// 5th-generation tensor cores (tcgen05 + TMEM), the exact pair arithmetic on the CUDA cores for the few
-// pairs that pass.
+// psim_allpairs_tc.cuh — the all-pairs force pass with the distance filter as ONE kind::f16 tcgen05.mma per
+// tile, FP16 accumulators in TMEM, packed TMEM loads and a sign test.
 //
-// Mathematics.  The conservative filter of psim_allpairs2.cuh,
-//     est(i, j) = w_j + y_i . (-2 y_j)  <  cut_i ,      y = position relative to the box centre,
-// is one entry of a Gram matrix: row i of A = (y_i, 1), row j of B = (-2 y_j, w_j).  A block owns M = 128
-// i-particles (the rows of the accumulator, one TMEM lane each) and walks the j records in tiles of N2 = 128.
-// TF32 keeps 11 significand bits, far too few for coordinates of ~100 and a cutoff of 2.5, so each float is
-// split into two TF32 pieces (x = x1 + x2 + r, |r| < 2^-20 |x|) and K carries the three largest cross
-// products per coordinate:
-//     A row: x1 x1 x2 | y1 y1 y2 | z1 z1 z2 | 1  1  1  | 0 0 0 0      (K = 16 = two MMAs of K = 8)
-//     B row: X1 X2 X1 | Y1 Y2 Y1 | Z1 Z2 Z1 | w1 w2 w3 | 0 0 0 0      (X = -2 x ...)
-// All products are exact (11 x 11 bits) and the tensor core accumulates in FP32, so est differs from the
-// packed-FP32 filter's value by the dropped terms (< 2^-18 (|y_i|^2 + |y_j|^2)) plus accumulation rounding;
-// the weight's relative margin is 256 u (u = 2^-24) to cover both, and an absolute term 16 u r_cut (|y| + 1)
-// covers the rounding of the coordinates themselves (tests/test_filter_math.py restates this in numpy and
-// checks the margin under a worst-case accumulation model).  Coordinates are taken relative to the box
-// centre: the margins scale with |y|^2, so this quarters the false positives of a corner particle.  The
-// filter only ever passes EXTRA pairs; every pair that passes is decided and evaluated exactly, in the
-// working precision, with the reference's own arithmetic (pair_force, psim_common.cuh) — and the kernel
-// counts the ordered in-range pairs it evaluated, which the tests compare with the exact O(N^2) count.
+// Why FP16 (measured on B200, tools/microbench/tc_f16.cu, profiles/r2_microbench_tc_f16.log).  In round 2's first,
+// TF32 form of this kernel (split-TF32 operands, FP32 accumulators; git history) a tile of 128 x 128 pair tests costs 128 cycles of tensor pipe (two K = 8 MMAs), and
+// 128 cycles of ALU pipe per SM sub-partition (16 FMNMX3 per 32 values, one every 2 clocks).  With FP16
+// operands the same K = 16 product is ONE instruction at twice the rate (64 cycles per tile); with an FP16
+// accumulator tcgen05.ld .pack::16b delivers two entries per register, so the reduction handles two pairs per
+// lane-operation (64 cycles per tile).  The tensor core forms the 16-term sum at (about) FP32 width and rounds
+// once (measured: error 3.4e-5 on sums whose terms are ~350), so the cancellation |y_i|^2 + |y_j|^2 - 2 y_i.y_j
+// survives; the FP16 rounding of the RESULT only has to keep its sign.
 //
-// Organisation (one block of 21 warps per SM; all 512 TMEM columns as four 128-column accumulators):
-//   * tc_prepare_kernel builds the B operand ONCE per force pass, in global memory, already in the UMMA
-//     shared-memory tile layout (8 KB per tile of 128 j records);
-//   * a producer warp streams those tiles into a 4-slot shared-memory ring with TMA bulk copies
-//     (cp.async.bulk, completion on an mbarrier, 16 KB = two tiles per copy);
-//   * four MMA warps (one elected lane each, one accumulator each) issue the tcgen05.mma pairs — one
-//     thread doing all of it sustains only ~1 tile per 950 cycles (measured, tools/microbench/tc_gram.cu);
-//   * sixteen consumer warps read their 32 rows x 32 columns of every tile with one tcgen05.ld.32x32b.x32,
-//     hand the accumulator back, reduce the 32 values with 16 three-input minima and compare with cut_i.
-//     The consumer tile loop is a function of its own (consume_tiles) so that ptxas gives it a register
-//     allocation with two sets of 32 values: the load of tile t + 1 is in flight while tile t is reduced.
-//     Rare hits go to a per-thread 16-bit queue in shared memory; the exact path runs between calls of
-//     consume_tiles, never while an accumulator is held;
-//   * rings of mbarriers (B full/empty, accumulator full/empty) replace every block-wide barrier;
-//   * j-split: when a launch has too few i-blocks to fill the SMs evenly (a shard of a multi-GPU run, a
-//     small N) the j range is cut into S segments, one block each; the partial forces of an i-block meet
-//     in global scratch and the block that arrives last adds them in segment order (fixed order, so the
-//     result is run-to-run identical) and runs the kick/drift epilogue.
+// Mathematics.  With y = position relative to the box centre, scaled by a power of two S so that |S y|^2 fits
+// FP16, every float is split into two FP16 pieces (11 significant bits each), weights into three:
+//     A row i: x1 x1 x2 | y1 y1 y2 | z1 z1 z2 | 1  1  1  | -C1 -C2 -C3 | 0
+//     B row j: X1 X2 X1 | Y1 Y2 Y1 | Z1 Z2 Z1 | w1 w2 w3 |  1   1   1  | 0        X = -2 S x_j ...
+//     acc(i, j) = w_j - 2 S^2 y_i.y_j - C_i ,   C_i = S^2 r_cut^2 (1 + d) - w_i ,   w = S^2 |y|^2 (1 - k) - a
+// so acc < 0 is the filter's "may be in range".  k = 2^-16 covers the dropped cross terms
+// (<= 3 * 2^-22 (|Sy_i|^2 + |Sy_j|^2)) and the accumulation error with a factor > 5 to spare; a covers the rounding of
+// the coordinates to float (16 u r_cut (|y| + 1), as in the TF32 kernel) plus 2^-13 for FP16 underflow of the
+// smallest pieces and of the result.  Inactive and padding records get a row that can never pass (+60000);
+// a particle so far outside the box that S^2 |y|^2 would overflow FP16 (it left the box and the next rebuild
+// will deactivate it) gets a row that ALWAYS passes (-60000): every pair that passes is decided and evaluated
+// exactly, in the working precision, by the exact path (exact_pair -> pair_force, psim_common.cuh), so the
+// forces are unchanged; the kernel counts the in-range pairs it evaluated for the tests' audit.
+//
+// Organisation (one block of 21 warps per SM, four 128-column FP16 accumulators in TMEM):
+//   * tc_prepare_kernel writes every particle's B row (32 B) once per force pass in UMMA tile layout;
+//   * the TMA producer streams 32 KB (eight tiles) per bulk copy through a 2-slot ring;
+//   * MMA warp w issues the tiles t = w (mod 4) into accumulator w: one instruction and one commit per tile,
+//     one b_full wait per two tiles (the B slot is handed back by a consumer lane, not by a second commit);
+//   * consumer warps split by tile parity: eight warps (4 lane quadrants x 2 column halves) take the even
+//     tiles, eight the odd ones; a warp reads its 32 rows x 64 columns with one tcgen05.ld.32x32b.x32.pack::16b,
+//     releases the accumulator at once and only then ORs the 32 packed registers (16 LOP3): any sign bit set =
+//     a candidate; rare hits go to the 16-bit queue.
+//   * j-split: when a launch has too few i-blocks to fill the SMs evenly (a shard of a multi-GPU run, a small N)
+//     the j range is cut into S segments, one block each; the partial forces of an i-block meet in global scratch
+//     and the block that arrives last adds them in segment order (fixed order: run-to-run identical results) and
+//     runs the kick/drift epilogue.
+//   * TMA bulk copies here read this GPU's own memory only (the B rows are rebuilt locally after the all-gather).
 #pragma once
 
+#include <cuda_fp16.h>
+
 #include "psim_allpairs.cuh"
-#include "psim_allpairs2.cuh"
 
 namespace psim {
 namespace tc {
 
-constexpr int M = 128;                          // i-particles per block = accumulator rows = TMEM lanes
-constexpr int K = 16;                           // split-TF32 inner dimension (two MMAs of K = 8)
-constexpr int N2 = 128;                         // j records per tile = accumulator columns per buffer
-constexpr int NBUF = 512 / N2;                  // TMEM ring: four accumulators of 128 columns
-constexpr int NCTL = NBUF;                      // MMA warps: warp w owns accumulator w, tiles t = w (mod NCTL)
-constexpr int NPAIR = 4;                        // shared-memory ring: 4 slots of two tiles (one 16 KB bulk copy each)
-// NPAIR must be EVEN.  Tile pair P lives in slot P % NPAIR and is consumed by MMA warps 0,1 (P even) or 2,3
-// (P odd).  With an odd ring (round 1's experimental kernel had 3) consecutive phases of a slot's b_full
-// barrier belong to ALTERNATING warp sets: a warp waits on phase n and next on phase n + 2, the same parity.
-// mbarrier.try_wait.parity(p) only says "the phase with parity p is over", so whenever the copy of phase
-// n + 1 had not landed yet the wait for n + 2 passed at once: the warp multiplied a stale tile and arrived on
-// b_empty a phase early (round 1's intermittent launch failure / hang).  With an even ring a slot is always
-// used by the same warp set, phase after phase.
-static_assert(NPAIR % 2 == 0, "odd ring: phase-parity aliasing on b_full (see above)");
-constexpr int STAGES = 2 * NPAIR;               // 8 x 8 KB
-constexpr int TILE_BYTES = N2 * K * 4;          // 8 KB
-constexpr int NQ = 4;                           // column groups: warp w reads TMEM lanes 32 (w % 4).., columns 32 (w / 4)..
-constexpr int CW = 4 * NQ;                      // consumer warps
-constexpr int TW = 32 * (CW + NCTL + 1);        // + the MMA warps + the TMA producer warp
-constexpr int QC = 96;                          // logical capacity of a consumer thread's candidate queue ...
-constexpr int QPHYS = QC + 32;                  // ... + room for one tile's unbounded first pass (queue_chunk): 128 KB in all
-constexpr int QMAX_TILE = 5;                    // logical entries one tile can add: up to 5 columns, or 1 dense chunk
-constexpr int QSTRIDE = 32 * CW;                // entry e of thread tid at q[e * QSTRIDE + tid] (16-bit): conflict-free
-constexpr int SEG = 1024;                       // tiles per consume_tiles call: a queue entry holds a 10-bit tile offset
-constexpr int RING_BYTES = STAGES * TILE_BYTES;
-constexpr int SMEM_BYTES = RING_BYTES + QPHYS * QSTRIDE * 2;
-constexpr unsigned DENSE = 0x8000u;             // queue entry: [dense:1][tile - t_begin:10][column:5]; dense = all 32 columns
 constexpr int MAX_JSPLIT = 8;                   // j segments per i-block (launch-time choice)
+
+
+constexpr int M = 128;                          // i-particles per block = accumulator rows = TMEM lanes
+constexpr int K = 16;                           // FP16 inner dimension: one MMA
+constexpr int N2 = 128;                         // j records per tile = accumulator columns per buffer
+constexpr int NBUF = 4;                         // TMEM ring: four accumulators of 128 columns
+constexpr int NCTL = NBUF;                      // MMA warps
+constexpr int TILE_BYTES = N2 * K * 2;          // 4 KB
+constexpr int TPS = 8;                          // tiles per ring slot (one 32 KB bulk copy)
+constexpr int NSLOT = 2;
+constexpr int SLOT_BYTES = TPS * TILE_BYTES;
+constexpr int RING_BYTES = NSLOT * SLOT_BYTES;  // 64 KB
+constexpr int CW = 16;                          // consumer warps: (tile parity) x (4 lane quadrants) x (2 column halves)
+constexpr int TW = 32 * (CW + NCTL + 1);
+constexpr int QC = 64, QPHYS = QC + 64;         // queue: logical capacity + one chunk's unbounded first pass (64 columns)
+constexpr int QMAX_TILE = 5;
+constexpr int QSTRIDE = 32 * CW;
+constexpr int SEG = 512;                        // own tiles per consume call: a queue entry holds a 9-bit tile offset
+constexpr int SMEM_BYTES = RING_BYTES + QPHYS * QSTRIDE * 2;   // 64 KB + 128 KB
+constexpr unsigned DENSE = 0x8000u;             // queue entry: [dense:1][own tile - k_begin:9][column:6]
+constexpr float BIG = 60000.0f;                 // fits FP16; larger than any S^2 |y|^2 the scaling admits
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
-// rows x 16 tf32 as two K-blocks of 8; inside a K-block 8-row groups are 256 B apart (SBO) and the
-// two 16-byte K-chunks of a row 128 B apart (LBO); rows of a group 16 B apart: the canonical
-// K-major SWIZZLE_NONE layout of a UMMA shared-memory descriptor.
-__device__ __forceinline__ unsigned chunk_off(int rows, int r, int chunk) {   // chunk = k / 4, 0..3
-  return (unsigned)((chunk >> 1) * rows * 32 + (r >> 3) * 256 + (chunk & 1) * 128 + (r & 7) * 16);
-}
+
 __device__ __forceinline__ unsigned long long make_desc(unsigned addr) {
   const unsigned long long lbo = 128 >> 4, sbo = 256 >> 4;
   return (unsigned long long)((addr >> 4) & 0x3FFF) | (lbo << 16) | (sbo << 32) | (1ull << 46);   // version 1 (sm_100)
 }
 
-__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
-__device__ __forceinline__ void split2(float x, float& a, float& b) { a = tf32_hi(x); b = tf32_hi(x - a); }
-__device__ __forceinline__ void split3(float x, float& a, float& b, float& c) {
-  a = tf32_hi(x); const float r = x - a; b = tf32_hi(r); c = tf32_hi(r - b);
-}
-
-// Filter record of one particle: float coordinates RELATIVE TO THE BOX CENTRE and the weight with the
-// tensor-core path's margins (header).  The subtraction is done in the working precision.
-template <class R>
-__device__ __forceinline__ FilterRec filter_record_tc(const Real4<R>& p, const Consts<R>& c, float rcut) {
-  constexpr float u32 = 5.9604645e-8f;
-  FilterRec f;
-  f.x = (float)r_sub(p.x, r_mul((R)0.5, c.area[0]));
-  f.y = (float)r_sub(p.y, r_mul((R)0.5, c.area[1]));
-  f.z = (float)r_sub(p.z, r_mul((R)0.5, c.area[2]));
-  const float n2 = f.x * f.x + f.y * f.y + f.z * f.z;
-  f.w = n2 * (1.0f - 256.0f * u32) - 16.0f * u32 * rcut * (sqrtf(n2) + 1.0f);
-  if (p.w >= c.huge) f.w = 1.0e30f;          // inactive or padding: never a candidate
-  return f;
-}
 
 __device__ __forceinline__ void mbar_init(unsigned addr, unsigned count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(addr), "r"(count));
@@ -145,37 +114,6 @@ __device__ __forceinline__ void umma_commit(unsigned mbar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(mbar) : "memory");
 }
 
-#define PSIM_TMEM_LD32(r, taddr)                                                                                   \
-  asm volatile(                                                                                                    \
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                    \
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                                    \
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"                  \
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),            \
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),      \
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),    \
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])     \
-      : "r"(taddr))
-
-// B operand rows of all particles, tile by tile, in the canonical layout of chunk_off(); also clears the
-// pair counter of the force kernel that follows.
-template <class R>
-__global__ void __launch_bounds__(256)
-tc_prepare_kernel(const Real4<R>* __restrict__ pos, unsigned char* __restrict__ bops, int64_t n_pad, Consts<R> c,
-                  unsigned long long* __restrict__ pair_count) {
-  const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (j == 0) *pair_count = 0ull;                  // the force kernel that follows counts what its exact path evaluates
-  if (j >= n_pad) return;
-  const FilterRec f = filter_record_tc(pos[j], c, (float)c.r_cut);
-  float x1, x2, y1, y2, z1, z2, w1, w2, w3;
-  split2(-2.0f * f.x, x1, x2); split2(-2.0f * f.y, y1, y2); split2(-2.0f * f.z, z1, z2);
-  split3(f.w, w1, w2, w3);
-  unsigned char* b = bops + (j / N2) * TILE_BYTES;
-  const int r = (int)(j % N2);
-  *reinterpret_cast<float4*>(b + chunk_off(N2, r, 0)) = make_float4(x1, x2, x1, y1);
-  *reinterpret_cast<float4*>(b + chunk_off(N2, r, 1)) = make_float4(y2, y1, z1, z2);
-  *reinterpret_cast<float4*>(b + chunk_off(N2, r, 2)) = make_float4(z1, w1, w2, w3);
-  *reinterpret_cast<float4*>(b + chunk_off(N2, r, 3)) = make_float4(0.f, 0.f, 0.f, 0.f);
-}
 
 // The exact path: one queued candidate j of row ig in the working precision, with the reference's own
 // arithmetic (pair_force, psim_common.cuh).
@@ -203,61 +141,152 @@ __device__ __forceinline__ unsigned q_load(unsigned qaddr, int e) {
   return v;
 }
 
-// What the exact path needs, kept on the kernel's stack so that consume_tiles carries ONE pointer for it.
+
+// Scratch of the j-split (S > 1): partial forces of every (i-block, segment) and one arrival counter per
+// i-block (zero between launches: the combining block clears it).
 template <class R>
-struct FlushCtx {
-  const Real4<R>* pos; const Consts<R>* c; int64_t ig;
-  int64_t col0;              // global index of the first column of this thread's group in tile 0 of the block's j segment
-  R f[3]; unsigned in_range; // force on row ig; ordered in-range pairs evaluated
+struct JSplit {
+  int S;                     // segments per i-block (1: no split, scratch unused)
+  R* part;                   // [gridDim.x][3][M]
+  unsigned* arrived;         // [i-blocks]
 };
 
-// seg_begin: the tile (relative to the block's j segment) that queue codes are relative to.
-template <class R>
-__device__ __noinline__ void flush_queue(FlushCtx<R>* x, unsigned q, int cnt, int seg_begin) {
-  if (cnt == 0) return;                            // rows past i_hi / inactive rows never queue anything
-  const Real4<R>* __restrict__ pos = x->pos;
-  const Consts<R>& c = *x->c;
-  const int64_t ig = x->ig;
-  const Real4<R> pi = pos[ig];
-  for (int e = 0; e < cnt; ++e) {
-    const unsigned v = q_load(q, e);
-    const int64_t j0 = (int64_t)(seg_begin + (int)((v >> 5) & 1023u)) * N2 + x->col0;
-    if (v & DENSE) {
-      for (int u = 0; u < 32; ++u) exact_pair(pos, c, ig, pi, j0 + u, x->f, &x->in_range);
-    } else {
-      exact_pair(pos, c, ig, pi, j0 + (int64_t)(v & 31u), x->f, &x->in_range);
-    }
-  }
+
+// rows x 16 halves (32 B per row): 8-row groups 256 B apart (SBO), the two 16-byte K-chunks of a row 128 B
+// apart (LBO), rows of a group 16 B apart: byte-identical to one K = 8 block of the TF32 layout.
+__device__ __forceinline__ unsigned chunk_off16(int r, int chunk) {   // chunk = k / 8, 0..1
+  return (unsigned)((r >> 3) * 256 + chunk * 128 + (r & 7) * 16);
 }
 
-__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(a, fminf(b, c)); }   // one FMNMX3
+struct alignas(16) Half8 { __half2 a, b, c, d; };
 
-// 32 columns of this thread's row: 16 three-input minima (groups of 9, 9, 9 and 5 columns), one compare.
-// The rare hit pushes the columns below cut (tile-relative code `tcode`); more than QMAX_TILE of them are
-// replaced by ONE dense entry, so a tile adds at most QMAX_TILE logical entries (what lets consume_tiles
-// bound the queue) — the first pass may write up to 32 entries past cnt, hence QPHYS.
-__device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], float cut, unsigned tcode, unsigned q, int& cnt) {
-  float mg[4];
-#pragma unroll
-  for (int g = 0; g < 3; ++g) {
-#define PSIM_V(k) __uint_as_float(r[9 * g + (k)])
-    mg[g] = min3f(min3f(PSIM_V(0), PSIM_V(1), PSIM_V(2)), min3f(PSIM_V(3), PSIM_V(4), PSIM_V(5)), min3f(PSIM_V(6), PSIM_V(7), PSIM_V(8)));
-#undef PSIM_V
+__device__ __forceinline__ void hsplit2(float x, __half& a, __half& b) {
+  a = __float2half_rn(x); b = __float2half_rn(x - __half2float(a));
+}
+__device__ __forceinline__ void hsplit3(float x, __half& a, __half& b, __half& c) {
+  a = __float2half_rn(x); const float r = x - __half2float(a);
+  b = __float2half_rn(r); c = __float2half_rn(r - __half2float(b));
+}
+
+// The scale: the largest power of two S with (1.4 x half diagonal of the box x S)^2 <= 60000, so that anything
+// inside the box, and well outside it, has a finite FP16 weight.  Computed on the host.
+struct Scale16 { float S, S2; };
+
+// What one particle contributes to the operands.  kind: 0 = normal, 1 = never passes (inactive, padding),
+// 2 = always passes (beyond the FP16 range).
+struct Rec16 { float x, y, z, w; int kind; };
+
+template <class R>
+__device__ __forceinline__ Rec16 filter_record_tc(const Real4<R>& p, const Consts<R>& c, float rcut, Scale16 sc) {
+  constexpr float u32 = 5.9604645e-8f;
+  Rec16 f;
+  const float fx = (float)r_sub(p.x, r_mul((R)0.5, c.area[0]));
+  const float fy = (float)r_sub(p.y, r_mul((R)0.5, c.area[1]));
+  const float fz = (float)r_sub(p.z, r_mul((R)0.5, c.area[2]));
+  const float n2 = fx * fx + fy * fy + fz * fz;
+  f.x = fx * sc.S; f.y = fy * sc.S; f.z = fz * sc.S;
+  const float n2s = n2 * sc.S2;
+  f.w = n2s * (1.0f - 1.52587890625e-5f) - sc.S2 * 16.0f * u32 * rcut * (sqrtf(n2) + 1.0f) - 1.220703125e-4f;
+  f.kind = 0;
+  if (!(n2s < 0.9f * BIG)) f.kind = 2;         // also catches NaN / inf coordinates
+  if (p.w >= c.huge) f.kind = 1;
+  return f;
+}
+
+// B operand rows of all particles, tile by tile (4 KB per 128 records), in the layout of chunk_off16(); also
+// clears the pair counter of the force kernel that follows.
+template <class R>
+__global__ void __launch_bounds__(256)
+tc_prepare_kernel(const Real4<R>* __restrict__ pos, unsigned char* __restrict__ bops, int64_t n_pad, Consts<R> c,
+                    Scale16 sc, unsigned long long* __restrict__ pair_count) {
+  const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (j == 0) *pair_count = 0ull;
+  if (j >= n_pad) return;
+  const Rec16 f = filter_record_tc(pos[j], c, (float)c.r_cut, sc);
+  const __half zero = __float2half_rn(0.f), one = __float2half_rn(1.f);
+  __half x1 = zero, x2 = zero, y1 = zero, y2 = zero, z1 = zero, z2 = zero, w1, w2 = zero, w3 = zero;
+  if (f.kind == 0) {
+    hsplit2(-2.0f * f.x, x1, x2); hsplit2(-2.0f * f.y, y1, y2); hsplit2(-2.0f * f.z, z1, z2);
+    hsplit3(f.w, w1, w2, w3);
+  } else {
+    w1 = __float2half_rn(f.kind == 1 ? BIG : -BIG);
   }
-  mg[3] = min3f(min3f(__uint_as_float(r[27]), __uint_as_float(r[28]), __uint_as_float(r[29])), __uint_as_float(r[30]),
-                __uint_as_float(r[31]));
-  const float m = fminf(min3f(mg[0], mg[1], mg[2]), mg[3]);
-  if (m < cut) {
+  unsigned char* b = bops + (j / N2) * TILE_BYTES;
+  const int r = (int)(j % N2);
+  Half8 c0, c1;
+  c0.a = __halves2half2(x1, x2); c0.b = __halves2half2(x1, y1); c0.c = __halves2half2(y2, y1); c0.d = __halves2half2(z1, z2);
+  c1.a = __halves2half2(z1, w1); c1.b = __halves2half2(w2, w3); c1.c = __halves2half2(one, one); c1.d = __halves2half2(one, zero);
+  *reinterpret_cast<Half8*>(b + chunk_off16(r, 0)) = c0;
+  *reinterpret_cast<Half8*>(b + chunk_off16(r, 1)) = c1;
+}
+
+// A operand row of one i-particle (same record, the other role).
+__device__ __forceinline__ void store_a_row(unsigned char* sA, int row, const Rec16& f, float cut2s) {
+  const __half zero = __float2half_rn(0.f), one = __float2half_rn(1.f);
+  __half x1 = zero, x2 = zero, y1 = zero, y2 = zero, z1 = zero, z2 = zero, o = zero, c1 = zero, c2 = zero, c3 = zero;
+  if (f.kind == 0) {
+    hsplit2(f.x, x1, x2); hsplit2(f.y, y1, y2); hsplit2(f.z, z1, z2);
+    hsplit3(-(cut2s - f.w), c1, c2, c3);
+    o = one;
+  } else {
+    c1 = __float2half_rn(f.kind == 1 ? BIG : -BIG);      // times the 1 in column 12 of every B row
+  }
+  Half8 a0, a1;
+  a0.a = __halves2half2(x1, x1); a0.b = __halves2half2(x2, y1); a0.c = __halves2half2(y1, y2); a0.d = __halves2half2(z1, z1);
+  a1.a = __halves2half2(z2, o); a1.b = __halves2half2(o, o); a1.c = __halves2half2(c1, c2); a1.d = __halves2half2(c3, zero);
+  *reinterpret_cast<Half8*>(sA + chunk_off16(row, 0)) = a0;
+  *reinterpret_cast<Half8*>(sA + chunk_off16(row, 1)) = a1;
+}
+
+#define PSIM_TMEM_LD32_PACK16(r, taddr)                                                                            \
+  asm volatile(                                                                                                    \
+      "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "                                                          \
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                                    \
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"                  \
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),            \
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),      \
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),    \
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])     \
+      : "r"(taddr))
+
+constexpr unsigned SIGNS = 0x80008000u;
+
+// -DPSIM_TC_PROF: clock64 timeline of block 0 (tiles 0..511), printed at the end of the kernel.
+// events: 0..3 per MMA warp: [4 w + 0] b_full/d_empty seen, [4 w + 1] issued + committed;
+//         16 + 3 * consumer warp + {0: d_full seen, 1: load complete, 2: accumulator released}
+#ifdef PSIM_TC_PROF
+__device__ long long g_trace[16 + 3 * CW][512];
+#define TR(ev, tile) { if (blockIdx.x == 0 && (tile) < 512) g_trace[ev][tile] = clock64(); }
+#else
+#define TR(ev, tile) {}
+#endif
+
+// 64 columns of this thread's row as 32 packed registers (low half = even column): OR them (16 LOP3,
+// groups of 9, 9, 9 and 5 registers); a sign bit in the result = some entry is negative = a candidate.
+// The rare hit pushes the negative columns (tile-relative code `tcode`); more than QMAX_TILE of them become
+// ONE dense entry, so a chunk adds at most QMAX_TILE logical entries — the first pass may write up to 64
+// entries past cnt, hence QPHYS.
+__device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], unsigned tcode, unsigned q, int& cnt) {
+  // grouped tree (9, 9, 9, 5 registers) and an unrolled descent into the groups
+  unsigned mg[4];
+#pragma unroll
+  for (int g = 0; g < 3; ++g)
+    mg[g] = (r[9 * g] | r[9 * g + 1] | r[9 * g + 2]) | (r[9 * g + 3] | r[9 * g + 4] | r[9 * g + 5]) |
+            (r[9 * g + 6] | r[9 * g + 7] | r[9 * g + 8]);
+  mg[3] = (r[27] | r[28] | r[29]) | r[30] | r[31];
+  const unsigned m = (mg[0] | mg[1] | mg[2]) | mg[3];
+  if (m & SIGNS) {
     const int c0 = cnt;
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
-      if (mg[g] < cut) {
+      if (mg[g] & SIGNS) {
 #pragma unroll
         for (int k = 0; k < 9; ++k) {
           const int u = 9 * g + k;                 // static after unrolling: r[] must stay in registers
-          if (u < 32 && __uint_as_float(r[u < 32 ? u : 0]) < cut) {
-            q_store(q, cnt, tcode + u);
-            ++cnt;
+          if (u < 32) {
+            const unsigned v = r[u < 32 ? u : 0];
+            if (v & 0x00008000u) { q_store(q, cnt, tcode + 2 * u); ++cnt; }
+            if (v & 0x80000000u) { q_store(q, cnt, tcode + 2 * u + 1); ++cnt; }
           }
         }
       }
@@ -269,122 +298,128 @@ __device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], float cut, 
   }
 }
 
-// The consumer tile loop, a function of its own so that ptxas gives it its own register allocation
-// (a few scalars + two sets of 32 accumulator values): the tcgen05.ld of tile t + 1 is in flight while
-// tile t is reduced.  tcgen05.wait::ld waits for ALL loads of the thread, hence the order
-// wait -> hand the accumulator back -> start the next load -> reduce.  Unrolled over the four accumulators
-// so that buffer offsets are immediates.
-// The loop state must live in UNIFORM registers (measured: with vector loop state ptxas wraps every wait in
-// divergence barriers and spills, 1.3x slower).  The tile count and the start tile arrive in vector
-// registers (function arguments), so both are passed through a warp reduction (REDUX writes a uniform
-// register) — they are the same in all lanes anyway.
-// Returns at a group boundary with no load in flight: at the end, every SEG tiles (a queue code holds a
-// 10-bit tile offset), and when some lane's queue could overflow during the next two groups (one is already
-// committed when the decision is taken).  The caller flushes the queue and calls again.  A flush in
-// mid-stream stalls the accumulator ring, so the capacity is sized to make the last kind rare.  The flush
-// is NOT called from here: values live across a call must sit above the callee chain's registers, and with
-// pair_force<double> below that left too few for this loop.
-// Returns (next tile << 32) | queue length.  Queue codes are relative to t_begin.  Tile numbers are relative
-// to the block's j segment.
-// dbar0: shared address of d_full[0]; d_empty[b] lives 8 * NBUF bytes after d_full[b].  nt: multiple of 8.
-__device__ __noinline__ unsigned long long consume_tiles(float cut, unsigned q, unsigned lane_base, unsigned dbar0, int nt_v, int t_begin_v) {
-  const int lane = threadIdx.x & 31;
-  const int t_begin = (int)__reduce_max_sync(0xffffffffu, (unsigned)t_begin_v);
-  const int nt = (int)__reduce_max_sync(0xffffffffu, (unsigned)nt_v);
-#define PSIM_TC_ACQUIRE(r, buf, par_)                                                            \
-  {                                                                                              \
-    mbar_wait_warp(dbar0 + 8u * (buf), (par_));   /* all lanes leave together: .aligned load next */ \
-    asm volatile("tcgen05.fence::after_thread_sync;");                                           \
-    PSIM_TMEM_LD32(r, lane_base + (unsigned)((buf) * N2));                                       \
+template <class R>
+struct FlushCtx {
+  const Real4<R>* pos; const Consts<R>* c; int64_t ig;
+  int64_t col0;              // global index of column 0 of this thread's chunk in ITS first tile of the block's j segment
+  R f[3]; unsigned in_range;
+};
+
+// k_begin: the own-tile index that queue codes are relative to; own tile k is tile 2 k + parity of the segment.
+template <class R>
+__device__ __noinline__ void flush_queue(FlushCtx<R>* x, unsigned q, int cnt, int k_begin) {
+  if (cnt == 0) return;
+  const Real4<R>* __restrict__ pos = x->pos;
+  const Consts<R>& c = *x->c;
+  const int64_t ig = x->ig;
+  const Real4<R> pi = pos[ig];
+  for (int e = 0; e < cnt; ++e) {
+    const unsigned v = q_load(q, e);
+    const int64_t j0 = (int64_t)(k_begin + (int)((v >> 6) & 511u)) * (2 * N2) + x->col0;
+    if (v & DENSE) {
+      for (int u = 0; u < 64; ++u) exact_pair(pos, c, ig, pi, j0 + u, x->f, &x->in_range);
+    } else {
+      exact_pair(pos, c, ig, pi, j0 + (int64_t)(v & 63u), x->f, &x->in_range);
+    }
   }
-#define PSIM_TC_RELEASE(buf)                                                                     \
-  {                                                                                              \
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");                                 \
-    asm volatile("tcgen05.fence::before_thread_sync;");   /* values are in registers */          \
-    __syncwarp();                                                                                \
-    if (lane == 0) mbar_arrive(dbar0 + 8u * (NBUF + (buf)));                                     \
-  }
-  unsigned rA[32], rB[32];
-  int cnt = 0, t0 = t_begin;
-  PSIM_TC_ACQUIRE(rA, 0, (unsigned)((t0 / NBUF) & 1))
-  for (;;) {
-    const unsigned par = (unsigned)((t0 / NBUF) & 1);
-    const unsigned tc0 = (unsigned)(t0 - t_begin) << 5;
-    // this group adds at most 4 QMAX_TILE logical entries, and so does the next one if we go on
-    const bool more = (t0 + NBUF < nt) && (t0 + NBUF - t_begin < SEG) &&
-                      !__any_sync(0xffffffffu, cnt > QC - 8 * QMAX_TILE);
-    PSIM_TC_RELEASE(0) PSIM_TC_ACQUIRE(rB, 1, par)
-    queue_chunk(rA, cut, tc0, q, cnt);
-    PSIM_TC_RELEASE(1) PSIM_TC_ACQUIRE(rA, 2, par)
-    queue_chunk(rB, cut, tc0 + 32u, q, cnt);
-    PSIM_TC_RELEASE(2) PSIM_TC_ACQUIRE(rB, 3, par)
-    queue_chunk(rA, cut, tc0 + 64u, q, cnt);
-    PSIM_TC_RELEASE(3)
-    if (more) PSIM_TC_ACQUIRE(rA, 0, par ^ 1u)
-    queue_chunk(rB, cut, tc0 + 96u, q, cnt);
-    t0 += NBUF;
-    if (!more) break;
-  }
-#undef PSIM_TC_ACQUIRE
-#undef PSIM_TC_RELEASE
-  return ((unsigned long long)(unsigned)t0 << 32) | (unsigned)cnt;
 }
 
-// Scratch of the j-split (S > 1): partial forces of every (i-block, segment) and one arrival counter per
-// i-block (zero between launches: the combining block clears it).
-template <class R>
-struct JSplit {
-  int S;                     // segments per i-block (1: no split, scratch unused)
-  R* part;                   // [gridDim.x][3][M]
-  unsigned* arrived;         // [i-blocks]
-};
+// The consumer tile loop of one warp (a function of its own, so that the exact path's double-precision
+// register needs stay out of it; loop state in uniform registers — see consume_tiles in psim_allpairs_tc.cuh).
+// The warp owns the tiles of one parity: own tile k is tile 2 k + p and lives in accumulator p + 2 (k & 1),
+// phase k >> 1.  Groups of four own tiles start at multiples of four, so the phase parities are immediates
+// (0, 0, 1, 1).  Per tile: wait for the accumulator, load the warp's 32 rows x 64 columns, HAND THE ACCUMULATOR
+// BACK, then reduce from registers.  What bounds this kernel is the round trip of an accumulator (consumers'
+// release -> MMA warp wakes -> issue -> tensor pipe -> commit -> consumers wake -> load; ~1000 cycles measured
+// with the reduction inside it, tools/tc_timeline.py): 512 TMEM columns per round trip is all the tensor pipe
+// gets, so the release comes as early as the data allows and the reduction of tile k overlaps the MMA side
+// of the next round instead of delaying it.
+// lane_base addresses the warp's 64 columns of accumulator p; accumulator p + 2 is 256 columns further.
+// dbar: shared address of d_full[p]; d_full[p + 2] is 16 bytes further, d_empty[b] 8 * NBUF bytes after
+// d_full[b].  releases_slots: this warp hands the ring slot of its tiles back to the TMA producer: lane 0
+// arrives on b_empty[(t / TPS) % NSLOT] once per own tile after the tile's d_full wait (the MMA that read the
+// B tile is complete then); bempty0 = shared address of b_empty[0].
+// ntk (own tiles): multiple of 4.  Returns (next own tile << 32) | queue length; queue codes are relative to
+// k_begin.  Returns at the end, every SEG own tiles, and when some lane's queue could overflow in the next group.
+__device__ __noinline__ unsigned long long consume_tiles(unsigned q, unsigned lane_base, unsigned dbar, unsigned bempty0,
+                                                           int releases_slots, int ntk_v, int k_begin_v) {
+  const int lane = threadIdx.x & 31;
+  const int k_begin = (int)__reduce_max_sync(0xffffffffu, (unsigned)k_begin_v);
+  const int ntk = (int)__reduce_max_sync(0xffffffffu, (unsigned)ntk_v);
+  const bool release_slot = __reduce_max_sync(0xffffffffu, (unsigned)releases_slots) != 0u;   // uniform
+  // own tile k = tile 2 k + p: its ring slot is ((2 k + p) / TPS) % NSLOT = (k / 4) % NSLOT for TPS = 8
+#define PSIM_TC_ORDER asm volatile("" : "+r"(r[0]), "+r"(r[9]), "+r"(r[18]), "+r"(r[27]));
+#define PSIM_TC_TILE(which, par_, kk, code)                                                    \
+  {                                                                                              \
+    mbar_wait_warp(dbar + 16u * (which), (par_));   /* all lanes leave together: .aligned load next */ \
+    if (lane == 0) TR(16 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
+    asm volatile("tcgen05.fence::after_thread_sync;");                                           \
+    PSIM_TMEM_LD32_PACK16(r, lane_base + (unsigned)((which) * 2 * N2));                          \
+    if (release_slot && lane == 0) mbar_arrive(bempty0 + 8u * (unsigned)(((kk) >> 2) % NSLOT)); \
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");                                 \
+    if (lane == 0) TR(17 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
+    asm volatile("tcgen05.fence::before_thread_sync;");   /* values are in registers */          \
+    __syncwarp();                                                                                \
+    if (lane == 0) mbar_arrive(dbar + 8u * NBUF + 16u * (which));                            \
+    if (lane == 0) TR(18 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
+    /* the reduction may not be scheduled ahead of the release: its first operands pass through here */ \
+    PSIM_TC_ORDER                                                                              \
+    queue_chunk(r, (code), q, cnt);                                                            \
+  }
+  unsigned r[32];
+  int cnt = 0, k0 = k_begin;
+  for (;;) {
+    const unsigned tc0 = (unsigned)(k0 - k_begin) << 6;
+    PSIM_TC_TILE(0, 0u, k0, tc0)
+    PSIM_TC_TILE(1, 0u, k0 + 1, tc0 + 64u)
+    PSIM_TC_TILE(0, 1u, k0 + 2, tc0 + 128u)
+    PSIM_TC_TILE(1, 1u, k0 + 3, tc0 + 192u)
+    k0 += 4;
+    // the next group adds at most 4 QMAX_TILE logical entries
+    if (k0 >= ntk || k0 - k_begin >= SEG || __any_sync(0xffffffffu, cnt > QC - 4 * QMAX_TILE)) break;
+  }
+#undef PSIM_TC_TILE
+  return ((unsigned long long)(unsigned)k0 << 32) | (unsigned)cnt;
+}
 
 template <class R, int MODE>
 __global__ void __launch_bounds__(TW, 1)
 allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, unsigned long long* __restrict__ pair_count,
-                   const JSplit<R> js) {
+                     const JSplit<R> js, const Scale16 sc) {
   extern __shared__ __align__(1024) unsigned char sB[];          // ring of B tiles, then the candidate queues
-  __shared__ __align__(128) unsigned char sA[M * K * 4];          // 8 KB
-  __shared__ __align__(8) unsigned long long b_full[NPAIR], b_empty[NPAIR], d_bar[2 * NBUF];   // d_bar: full[0..3], empty[0..3]
+  __shared__ __align__(128) unsigned char sA[M * K * 2];          // 4 KB
+  __shared__ __align__(8) unsigned long long b_full[NSLOT], b_empty[NSLOT], d_bar[2 * NBUF];   // d_bar: full[0..3], empty[0..3]
   unsigned long long* const d_full = d_bar;
   unsigned long long* const d_empty = d_bar + NBUF;
   __shared__ unsigned tmem_base_s;
   __shared__ int last_s;
-  __shared__ R fpart[NQ][3][M];
+  __shared__ R fpart[4][3][M];
 
   const Consts<R>& c = a.c;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool consumer = warp < CW;
   const int row = (warp & 3) * 32 + lane;          // accumulator row = TMEM lane (consumers)
-  const int half = (warp >> 2) % NQ;               // which 32 columns of every tile (consumers)
+  const int grp = (warp >> 2) & 3;                 // consumers: tile parity (grp >> 1) and column half (grp & 1)
+  const int par = grp >> 1, half64 = grp & 1;
   const int S = js.S;
   const int ib = (int)blockIdx.x / S, seg = (int)blockIdx.x - ib * S;
   const int64_t ig = a.i_lo + (int64_t)ib * M + row;
   const float rcut = (float)c.r_cut;
-  const float cut2f = (float)c.cut2_pad * (1.0f + 1.0e-6f);
-  // this block's j segment, in tiles (multiples of 8, so that every ring keeps its phase arithmetic)
+  const float cut2s = (float)c.cut2_pad * (1.0f + 1.0e-6f) * sc.S2;
+  // this block's j segment, in tiles (multiples of 8: whole ring slots, whole phase pairs)
   const int nt8 = (int)(a.n_pad / (8 * N2));
-  const int t_lo = 8 * ((seg * nt8) / S), t_hi = 8 * (((seg + 1) * nt8) / S);   // seg * nt8 < 2^31: nt8 = n_pad / 1024
+  const int t_lo = 8 * ((seg * nt8) / S), t_hi = 8 * (((seg + 1) * nt8) / S);
   const int nt = t_hi - t_lo;
 
-  // --- A tile (this block's i-particles) and the cut value of this thread's row ---
-  float cut = -1.0e30f;
-  if (consumer) {
-    FilterRec f; f.x = f.y = f.z = 0.f; f.w = 1.0e30f;
-    if (ig < a.i_hi) f = filter_record_tc(a.pos_cur[ig], c, rcut);
-    if (f.w < 1.0e30f) cut = cut2f - f.w;
-    if (half == 0) {
-      float x1, x2, y1, y2, z1, z2;
-      split2(f.x, x1, x2); split2(f.y, y1, y2); split2(f.z, z1, z2);
-      *reinterpret_cast<float4*>(sA + chunk_off(M, row, 0)) = make_float4(x1, x1, x2, y1);
-      *reinterpret_cast<float4*>(sA + chunk_off(M, row, 1)) = make_float4(y1, y2, z1, z1);
-      *reinterpret_cast<float4*>(sA + chunk_off(M, row, 2)) = make_float4(z2, 1.f, 1.f, 1.f);
-      *reinterpret_cast<float4*>(sA + chunk_off(M, row, 3)) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+  // --- A tile: this block's i-particles ---
+  if (consumer && grp == 0) {
+    Rec16 f; f.x = f.y = f.z = f.w = 0.f; f.kind = 1;
+    if (ig < a.i_hi) f = filter_record_tc(a.pos_cur[ig], c, rcut, sc);
+    store_a_row(sA, row, f, cut2s);
   }
   if (tid == 0) {
-    for (int s = 0; s < NPAIR; ++s) { mbar_init(smem_u32(&b_full[s]), 1); mbar_init(smem_u32(&b_empty[s]), 2); }
-    for (int b = 0; b < NBUF; ++b) { mbar_init(smem_u32(&d_full[b]), 1); mbar_init(smem_u32(&d_empty[b]), CW); }
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(smem_u32(&b_full[s]), 1); mbar_init(smem_u32(&b_empty[s]), TPS); }
+    for (int b = 0; b < NBUF; ++b) { mbar_init(smem_u32(&d_full[b]), 1); mbar_init(smem_u32(&d_empty[b]), CW / 2); }
     asm volatile("fence.mbarrier_init.release.cluster;");
   }
   if (warp == CW) {
@@ -397,76 +432,77 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
   asm volatile("tcgen05.fence::after_thread_sync;");
   const unsigned tm = tmem_base_s;
 
-  FlushCtx<R> fx;                                  // the exact path's state of this thread (consumers)
-  fx.pos = a.pos_cur; fx.c = &c; fx.ig = ig; fx.col0 = (int64_t)t_lo * N2 + half * 32;
+  FlushCtx<R> fx;
+  fx.pos = a.pos_cur; fx.c = &c; fx.ig = ig; fx.col0 = (int64_t)(t_lo + par) * N2 + half64 * 64;
   fx.f[0] = fx.f[1] = fx.f[2] = (R)0; fx.in_range = 0;
   if (warp == CW + NCTL) {
     if (lane == 0) {
-      // ===== TMA producer: one 16 KB bulk copy per pair of tiles, as far ahead as the ring allows =====
-      const int np = nt / 2;
+      // ===== TMA producer: one 32 KB bulk copy per eight tiles (this GPU's memory), as far ahead as the ring allows =====
+      const int nq = nt / TPS;
       const unsigned bfull0 = smem_u32(&b_full[0]), bempty0 = smem_u32(&b_empty[0]), sB0 = smem_u32(sB);
       const unsigned char* src = bops + (size_t)t_lo * TILE_BYTES;
-      for (int P = 0; P < np; ++P) {
-        const int s = P % NPAIR;
-        mbar_wait(bempty0 + 8u * s, (unsigned)(((P / NPAIR) & 1) ^ 1));   // both MMA warps done with the slot (fresh: passes)
-        mbar_expect_tx(bfull0 + 8u * s, 2 * TILE_BYTES);
-        bulk_copy_g2s(sB0 + (unsigned)(s * 2 * TILE_BYTES), src + (size_t)P * 2 * TILE_BYTES, 2 * TILE_BYTES, bfull0 + 8u * s);
+      for (int Q = 0; Q < nq; ++Q) {
+        const int s = Q % NSLOT;
+        mbar_wait(bempty0 + 8u * s, (unsigned)(((Q / NSLOT) & 1) ^ 1));   // all eight tiles of the slot multiplied (fresh: passes)
+        mbar_expect_tx(bfull0 + 8u * s, SLOT_BYTES);
+        bulk_copy_g2s(sB0 + (unsigned)(s * SLOT_BYTES), src + (size_t)Q * SLOT_BYTES, SLOT_BYTES, bfull0 + 8u * s);
       }
     }
   } else if (warp >= CW) {
     if (lane == 0) {
-      // ===== MMA warp w: issues the tiles t = w, w + NCTL, ... into accumulator w =====
+      // ===== MMA warp w: issues the tiles t = w, w + 4, ... into accumulator w: one instruction, one commit =====
       const int w = warp - CW;
-      const int ntw = (nt - w + NCTL - 1) / NCTL;
-      const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(N2 >> 3) << 17) | ((unsigned)(M >> 4) << 24);
-      const unsigned long long da0 = make_desc(smem_u32(sA)), da1 = make_desc(smem_u32(sA) + M * 32);
+      const int ntw = nt / NCTL;                   // nt is a multiple of 8
+      // D = F16 (c_format 0), A and B = F16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+      const unsigned idesc = ((unsigned)(N2 >> 3) << 17) | ((unsigned)(M >> 4) << 24);
+      const unsigned long long da = make_desc(smem_u32(sA));
       const unsigned acc = tm + (unsigned)(w * N2);
       const unsigned dfull = smem_u32(&d_full[w]), dempty = smem_u32(&d_empty[w]);
-      const unsigned bfull0 = smem_u32(&b_full[0]), bempty0 = smem_u32(&b_empty[0]), sB0 = smem_u32(sB);
+      const unsigned bfull0 = smem_u32(&b_full[0]), sB0 = smem_u32(sB);
       for (int k = 0; k < ntw; ++k) {
-        const int t = w + NCTL * k, P = t >> 1, s = P % NPAIR;
-        mbar_wait(bfull0 + 8u * s, (unsigned)((P / NPAIR) & 1));                        // tile pair landed
+        const int Q = k >> 1, s = Q % NSLOT;       // tile t = w + 4 k sits in ring fill Q = t / 8, at position w + 4 (k & 1)
+        if ((k & 1) == 0) mbar_wait(bfull0 + 8u * s, (unsigned)((Q / NSLOT) & 1));      // the slot's eight tiles landed
+        TR(4 * w + 2, w + 4 * k)
         mbar_wait(dempty, (unsigned)((k & 1) ^ 1));                                     // accumulator drained
+        TR(4 * w + 0, w + 4 * k)
         asm volatile("tcgen05.fence::after_thread_sync;");
-        const unsigned sb = sB0 + (unsigned)((2 * s + (t & 1)) * TILE_BYTES);
-#pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
-          const unsigned long long db = make_desc(sb + kb * N2 * 32);
-          asm volatile(
-              "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-              "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
-              :: "r"(acc), "l"(kb ? da1 : da0), "l"(db), "r"(idesc), "r"((unsigned)kb),
-                 "r"(0u), "r"(0u), "r"(0u), "r"(0u));
-        }
-        umma_commit(dfull);                       // both arrive when the two MMAs above have completed
-        umma_commit(bempty0 + 8u * s);
+        const unsigned long long db = make_desc(sB0 + (unsigned)(s * SLOT_BYTES + (w + 4 * (k & 1)) * TILE_BYTES));
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
+            :: "r"(acc), "l"(da), "l"(db), "r"(idesc), "r"(0u), "r"(0u), "r"(0u), "r"(0u), "r"(0u));
+        umma_commit(dfull);
+        TR(4 * w + 1, w + 4 * k)
       }
     }
   } else {
-    // ===== consumers: TMEM -> registers -> minimum against cut -> candidate queue; exact path between calls =====
-    const unsigned q = smem_u32(sB + RING_BYTES) + 2u * (unsigned)tid;     // this thread's queue, entry e at + e * 2 QSTRIDE bytes
-    const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(half * 32);
-    const unsigned dbar0 = smem_u32(&d_bar[0]);
-    int t = 0;
-    while (t < nt) {
-      const unsigned long long r = consume_tiles(cut, q, lane_base, dbar0, nt, t);
-      flush_queue<R>(&fx, q, (int)(unsigned)r, t);
-      t = (int)(r >> 32);
+    // ===== consumers =====
+    const unsigned q = smem_u32(sB + RING_BYTES) + 2u * (unsigned)tid;
+    const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(par * N2 + half64 * 64);
+    const unsigned dbar = smem_u32(&d_bar[par]);
+    const unsigned bempty0 = smem_u32(&b_empty[0]);
+    const int releases = ((warp & 3) == 0 && half64 == 0) ? 1 : 0;     // one warp per tile parity hands the ring slots back
+    const int ntk = nt / 2;
+    int k = 0;
+    while (k < ntk) {
+      const unsigned long long r = consume_tiles(q, lane_base, dbar, bempty0, releases, ntk, k);
+      flush_queue<R>(&fx, q, (int)(unsigned)r, k);
+      k = (int)(r >> 32);
     }
     unsigned in_range = fx.in_range;
     for (int off = 16; off > 0; off >>= 1) in_range += __shfl_xor_sync(0xffffffffu, in_range, off);
     if (lane == 0 && in_range) atomicAdd(pair_count, (unsigned long long)in_range);
   }
 
-  // --- the column groups of a row meet (fixed order) ---
+  // --- the four threads of a row meet (fixed order) ---
   asm volatile("tcgen05.fence::before_thread_sync;");
   R* const f = fx.f;
-  if (consumer && half > 0) { fpart[half][0][row] = f[0]; fpart[half][1][row] = f[1]; fpart[half][2][row] = f[2]; }
+  if (consumer && grp > 0) { fpart[grp][0][row] = f[0]; fpart[grp][1][row] = f[1]; fpart[grp][2][row] = f[2]; }
   __syncthreads();
-  const bool owner = consumer && half == 0;        // the thread that finishes row `row`
+  const bool owner = consumer && grp == 0;
   if (owner) {
 #pragma unroll
-    for (int g = 1; g < NQ; ++g) {
+    for (int g = 1; g < 4; ++g) {
       f[0] = r_add(f[0], fpart[g][0][row]); f[1] = r_add(f[1], fpart[g][1][row]); f[2] = r_add(f[2], fpart[g][2][row]);
     }
   }
@@ -474,8 +510,7 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
     __syncwarp();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tm));
   }
-  // --- the j segments of an i-block meet in global scratch; the block that arrives last adds them in
-  //     segment order and finishes the rows ---
+  // --- the j segments of an i-block meet in global scratch (psim_allpairs_tc.cuh) ---
   bool finish = true;
   if (S > 1) {
     if (owner) {
@@ -487,7 +522,7 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
     if (tid == 0) {
       const unsigned prev = atomicAdd(&js.arrived[ib], 1u);
       last_s = (prev == (unsigned)S - 1u) ? 1 : 0;
-      if (last_s) js.arrived[ib] = 0u;             // every segment has arrived: clean for the next launch
+      if (last_s) js.arrived[ib] = 0u;
     }
     __syncthreads();
     finish = last_s != 0;
@@ -501,6 +536,19 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
       }
     }
   }
+#ifdef PSIM_TC_PROF
+  __syncthreads();
+  if (blockIdx.x == 0 && tid == 0) {
+    const long long z = g_trace[2][256];
+    for (int t = 256; t < 268; ++t) {
+      const int w = t & 3, p = t & 1;
+      printf("TR t=%d mma: b_full %lld d_empty %lld committed %lld |", t, g_trace[4 * w + 2][t] - z, g_trace[4 * w][t] - z, g_trace[4 * w + 1][t] - z);
+      for (int cw = 8 * p; cw < 8 * p + 8; ++cw)
+        printf(" w%d: %lld %lld %lld", cw, g_trace[16 + 3 * cw][t] - z, g_trace[17 + 3 * cw][t] - z, g_trace[18 + 3 * cw][t] - z);
+      printf("\n");
+    }
+  }
+#endif
   R first = (R)0, second = (R)0;
   if (finish && owner && ig < a.i_hi) step_epilogue<R, MODE>(a, ig, f[0], f[1], f[2], first, second);
   if (MODE == MODE_FORCE_KICK_DRIFT) block_top2_store<R, TW>(first, second, a.top2_part, a.ticket, a.rank_pair);

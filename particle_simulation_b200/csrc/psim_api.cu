@@ -22,8 +22,8 @@
 
 #include "psim_allpairs.cuh"
 #include "psim_allpairs2.cuh"
+#include "psim_allpairs2.cuh"
 #include "psim_allpairs_tc.cuh"
-#include "psim_allpairs_tc16.cuh"
 #include "psim_cells.cuh"
 #include "psim_integrate.cuh"
 
@@ -191,8 +191,8 @@ class SimT final : public psim_sim {
   unsigned* tc_arrived = nullptr;       // ... j-split: arrival counter per i-block (zero between launches)
   int64_t tc_part_cap = 0;
   double* red_scratch = nullptr;        // 8 doubles: reductions of count_pairs / energy (no allocation per call)
-  bool attr_tc[3] = {false, false, false}, attr_tc16[3] = {false, false, false};
-  tch::Scale16 scale16 = {1.0f, 1.0f};
+  bool attr_tc[3] = {false, false, false};
+  tc::Scale16 scale16 = {1.0f, 1.0f};
   CellPath<R> cells;
   // options
   int algo = PSIM_FORCE_ALL_PAIRS;
@@ -256,8 +256,7 @@ class SimT final : public psim_sim {
     if (const char* e = std::getenv("PSIM_WARPS")) { const int v = std::atoi(e); if (v == 4 || v == 8 || v == 16) warps_forced = v; }
     if (const char* e = std::getenv("PSIM_ALLPAIRS_KERNEL")) {   // testing: run everything through one kernel
       const int v = std::atoi(e);
-      if (v == PSIM_ALLPAIRS_TENSOR || v == PSIM_ALLPAIRS_DIFFERENCE_FORM || v == PSIM_ALLPAIRS_CUDA_CORE || v == PSIM_ALLPAIRS_TENSOR_F16)
-        variant = v;
+      if (v == PSIM_ALLPAIRS_TENSOR || v == PSIM_ALLPAIRS_DIFFERENCE_FORM || v == PSIM_ALLPAIRS_CUDA_CORE) variant = v;
     }
     if (const char* e = std::getenv("PSIM_JSPLIT")) { const int v = std::atoi(e); if (v >= 1 && v <= tc::MAX_JSPLIT) jsplit_forced = v; }
     if (const char* e = std::getenv("PSIM_CLUSTER")) {
@@ -269,7 +268,7 @@ class SimT final : public psim_sim {
     {   // FP16 operand scale of the tensor-core filter: largest power of two with (1.4 x half diagonal x S)^2 <= 60000
       double d2 = 0;
       for (int d = 0; d < 3; ++d) d2 += p.length_of_area[d] * p.length_of_area[d];
-      const double lim = std::sqrt((double)tch::BIG) / (1.4 * 0.5 * std::sqrt(d2));
+      const double lim = std::sqrt((double)tc::BIG) / (1.4 * 0.5 * std::sqrt(d2));
       const float S = (float)std::ldexp(1.0, (int)std::floor(std::log2(lim)));
       scale16.S = S; scale16.S2 = S * S;
     }
@@ -436,7 +435,7 @@ class SimT final : public psim_sim {
       tc::JSplit<R> js;
       js.S = pick_jsplit(iblocks); js.part = nullptr; js.arrived = nullptr;
       *grid_out = iblocks * js.S;
-      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
+      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 2));   // 32 B per particle
       if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
       if (js.S > 1) {
         if (tc_part_cap < *grid_out) {
@@ -451,46 +450,14 @@ class SimT final : public psim_sim {
         }
         js.part = tc_part; js.arrived = tc_arrived;
       }
-      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, tc_pairs);
+      tc::tc_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, scale16, tc_pairs);
       ++launches;
-      // ring of B tiles + candidate queues (192 KB): also guarantees ONE block per SM — a block allocates
-      // all 512 TMEM columns, and no second block should ever wait inside tcgen05.alloc
       constexpr int kSmem = tc::SMEM_BYTES;
       if (!attr_tc[MODE]) {
         PSIM_CK(cudaFuncSetAttribute(tc::allpairs_tc_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
         attr_tc[MODE] = true;
       }
-      tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs, js);
-      return PSIM_OK;
-    }
-    if (variant == PSIM_ALLPAIRS_TENSOR_F16) {   // one kind::f16 MMA per tile, FP16 accumulators, packed loads
-      const int64_t iblocks = blocks(i_hi - i_lo, tc::M);
-      tc::JSplit<R> js;
-      js.S = pick_jsplit(iblocks); js.part = nullptr; js.arrived = nullptr;
-      *grid_out = iblocks * js.S;
-      if (!tc_bops) PSIM_CK(cudaMalloc(&tc_bops, (size_t)n_pad * tc::K * 4));
-      if (!tc_pairs) PSIM_CK(cudaMalloc(&tc_pairs, sizeof *tc_pairs));
-      if (js.S > 1) {
-        if (tc_part_cap < *grid_out) {
-          cudaFree(tc_part); tc_part = nullptr;
-          PSIM_CK(cudaMalloc(&tc_part, sizeof(R) * 3 * tc::M * (size_t)*grid_out));
-          tc_part_cap = *grid_out;
-        }
-        if (!tc_arrived) {
-          const size_t cnt = (size_t)blocks(shard, tc::M) + 1;
-          PSIM_CK(cudaMalloc(&tc_arrived, sizeof(unsigned) * cnt));
-          PSIM_CK(cudaMemsetAsync(tc_arrived, 0, sizeof(unsigned) * cnt, stream));
-        }
-        js.part = tc_part; js.arrived = tc_arrived;
-      }
-      tch::tc16_prepare_kernel<R><<<(unsigned)blocks(n_pad, 256), 256, 0, stream>>>(a.pos_cur, tc_bops, n_pad, c, scale16, tc_pairs);
-      ++launches;
-      constexpr int kSmem = tch::SMEM_BYTES;
-      if (!attr_tc16[MODE]) {
-        PSIM_CK(cudaFuncSetAttribute(tch::allpairs_tc16_kernel<R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        attr_tc16[MODE] = true;
-      }
-      tch::allpairs_tc16_kernel<R, MODE><<<(unsigned)*grid_out, tch::TW, kSmem, stream>>>(a, tc_bops, tc_pairs, js, scale16);
+      tc::allpairs_tc_kernel<R, MODE><<<(unsigned)*grid_out, tc::TW, kSmem, stream>>>(a, tc_bops, tc_pairs, js, scale16);
       return PSIM_OK;
     }
     if (variant == PSIM_ALLPAIRS_DIFFERENCE_FORM) {   // the literal reading of stoermer:117-121 in the working precision
@@ -703,7 +670,7 @@ class SimT final : public psim_sim {
     Control h;
     PSIM_CK(cudaMemcpyAsync(&h, ctrl, sizeof h, cudaMemcpyDeviceToHost, stream));
     unsigned long long fp = 0;
-    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && (variant == PSIM_ALLPAIRS_TENSOR || variant == PSIM_ALLPAIRS_TENSOR_F16) && tc_pairs;
+    const bool tracked = algo == PSIM_FORCE_ALL_PAIRS && variant == PSIM_ALLPAIRS_TENSOR && tc_pairs;
     if (tracked) PSIM_CK(cudaMemcpyAsync(&fp, tc_pairs, sizeof fp, cudaMemcpyDeviceToHost, stream));
     PSIM_CK(cudaStreamSynchronize(stream));
     out->filter_pairs = tracked ? (int64_t)fp : -1;
@@ -735,8 +702,7 @@ class SimT final : public psim_sim {
       case PSIM_OPT_ALLPAIRS_KERNEL:
         // 3 and 6 selected the round-1 tensor-core kernels: both are today's default
         if (value == 3 || value == 6) value = PSIM_ALLPAIRS_TENSOR;
-        if (value != PSIM_ALLPAIRS_TENSOR && value != PSIM_ALLPAIRS_DIFFERENCE_FORM && value != PSIM_ALLPAIRS_CUDA_CORE &&
-            value != PSIM_ALLPAIRS_TENSOR_F16)
+        if (value != PSIM_ALLPAIRS_TENSOR && value != PSIM_ALLPAIRS_DIFFERENCE_FORM && value != PSIM_ALLPAIRS_CUDA_CORE)
           return PSIM_ERR_INVALID_ARGUMENT;
         variant = (int)value; return PSIM_OK;
       default: return PSIM_ERR_INVALID_ARGUMENT;

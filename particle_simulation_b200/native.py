@@ -23,7 +23,7 @@ STATUS_OK = 0
 FORCE_ALL_PAIRS, FORCE_CELL_BINNED = 0, 1
 OPT_FORCE_ALGO, OPT_FUSED_STEP, OPT_KERNEL_TIMING, OPT_ALLPAIRS_KERNEL = 0, 1, 2, 3
 OPT_EXACT_DIFF_FILTER = OPT_ALLPAIRS_KERNEL      # round-1 name
-ALLPAIRS_TENSOR, ALLPAIRS_DIFFERENCE_FORM, ALLPAIRS_CUDA_CORE, ALLPAIRS_TENSOR_F16 = 0, 1, 5, 7
+ALLPAIRS_TENSOR, ALLPAIRS_DIFFERENCE_FORM, ALLPAIRS_CUDA_CORE = 0, 1, 5
 FRAME_SLOTS = 4
 
 

@@ -2,7 +2,7 @@
 -DPSIM_TC_PROF, selected through PSIM_LIBRARY): when each MMA warp saw its barriers and committed, when each
 consumer warp saw the accumulator, had it in registers and released it.
 
-    PSIM_LIBRARY=particle_simulation_b200/_build/libpsim_b200_prof.so python tools/tc_timeline.py [--variant 7] [--n 262144]
+    PSIM_LIBRARY=particle_simulation_b200/_build/libpsim_b200_prof.so python tools/tc_timeline.py [--variant 0] [--n 262144]
 """
 import argparse
 import os
@@ -15,7 +15,7 @@ from particle_simulation_b200 import generate as G       # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--variant", type=int, default=7)
+    ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--n", type=int, default=262144)
     ap.add_argument("--precision", type=int, default=8)
     args = ap.parse_args()
