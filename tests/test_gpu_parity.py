@@ -108,6 +108,34 @@ def test_k_steps_match_oracle(psim, oracle, precision, fused, algo, threads):
     sim.close()
 
 
+@pytest.mark.parametrize("algo", ["allpairs", "cells"])
+def test_rebuild_schedule_depends_on_nb_of_threads_like_the_reference(psim, oracle, algo):
+    """Two fast particles at the two ends of the array: with one trigger slice their displacements add up and
+    the rebuild fires at step 9; with NB_OF_THREADS = 3 they sit in different slices (program:305-323) and it
+    fires at step 13.  The device must follow the oracle step by step in both cases."""
+    ids, pos, vel = two_cubes()
+    vel = vel.copy()
+    vel[0] = (-30.0, 0.0, 0.0)
+    vel[-1] = (30.0, 0.0, 0.0)
+    first = {}
+    for threads in (1, 3):
+        o = oracle.Oracle(oracle.make_params(nb_of_threads=threads), 8, ids, pos, vel)
+        sim = psim.Simulation(psim.make_params(nb_of_threads=threads), ids, pos, vel, 8)
+        _select(psim, sim, algo)
+        for step in range(1, 31):
+            o.advance(1)
+            sim.advance(1)
+            assert sim.counters().rebuilds == o.rebuilds, "step %d, NB_OF_THREADS %d" % (step, threads)
+            if o.rebuilds and threads not in first:
+                first[threads] = step
+        _, x_ref, _, a_ref = o.frame()
+        _, x, _, a = sim.frame()
+        assert np.array_equal(a, a_ref) and np.abs(x - x_ref).max() <= XTOL[8]
+        sim.close()
+        o.close()
+    assert first[1] < first[3], "test lost its point: the schedules should differ (%r)" % (first,)
+
+
 @pytest.mark.parametrize("precision", [4, 8])
 @pytest.mark.parametrize("algo", ALGOS)
 def test_particles_leaving_the_box_are_deactivated_like_the_reference(psim, oracle, precision, algo):

@@ -39,6 +39,9 @@ def main():
             for scenario in ("calm", "leaving"):
                 for threads in (1, 3):        # NB_OF_THREADS: the reference's per-slice rebuild trigger (shipped: 3)
                     cases.append((precision, xtol, algo, scenario, threads))
+    for algo in ("allpairs", "cells"):
+        for threads in (1, 3):                # the one scenario whose rebuild schedule differs between 1 and 3 slices
+            cases.append((8, 1e-9, algo, "split_movers", threads))
     cases.append((8, 1e-9, "allpairs", "lattice_65536", 3))     # many i-blocks per rank, j-split, i_lo > 0
     cases.append((8, 1e-9, "cells", "lattice_65536", 1))
     for precision, xtol, algo, scenario, threads in cases:
@@ -46,6 +49,12 @@ def main():
             ids, pos, vel = two_cubes()
             kw = {}
             chunks = (1, 30, 29)
+        elif scenario == "split_movers":
+            # two fast particles at the two ends of the array: one trigger slice fires at step 9, three slices at 13
+            ids, pos, vel = two_cubes()
+            vel = vel.copy(); vel[0] = (-30.0, 0.0, 0.0); vel[-1] = (30.0, 0.0, 0.0)
+            kw = {}
+            chunks = (8, 1, 3, 1, 7)          # stops on both sides of steps 9 and 13
         elif scenario == "leaving":
             ids, pos, vel = two_cubes(side=4, speed=40.0, origin=3.0)
             kw = dict(length_of_area=(30.0, 30.0, 30.0), delta_t=0.002)
@@ -71,8 +80,10 @@ def main():
         good = True
         if sim.i_hi > sim.i_lo:
             good = np.abs(f0[sim.i_lo:sim.i_hi] - f0r[sim.i_lo:sim.i_hi]).max() <= ftol * np.abs(f0r).max()
+        schedule_ok = True
         for chunk in chunks:
             sim.advance(chunk); o.advance(chunk)
+            schedule_ok = schedule_ok and sim.counters().rebuilds == o.rebuilds
         _, x, v, a = sim.frame()
         _, xr, vr, ar = o.frame()
         # velocities: every rank fills its own slice; merge in rank order
@@ -83,7 +94,7 @@ def main():
         # the violent f32 scenario is chaotic beyond ~50 steps: flags and schedule only
         compare_xv = not (scenario == "leaving" and precision == 4)
         rebuilds = sim.counters().rebuilds
-        good = bool(good) and np.array_equal(a, ar) and rebuilds == o.rebuilds
+        good = bool(good) and schedule_ok and np.array_equal(a, ar) and rebuilds == o.rebuilds
         keep = ar.astype(bool)      # ejected particles carry |x| ~ 1e10: compare the active ones
         dx = np.abs(x[keep] - xr[keep]).max() if keep.any() else 0.0
         dv = np.abs(vm[keep] - vr[keep]).max() if keep.any() else 0.0
