@@ -583,7 +583,8 @@ def main():
                                "note": "ms_per_rebuild = (time of these steps - time of the same number of steps of "
                                        "the drift-free workload) / rebuilds"}
         if ans is not None:
-            ans_d = OracleAnswers(ids_d, pos_d, vel_d, area, prec, 120)     # long enough to cross two rebuilds
+            # long enough to cross rebuilds (one every ~50 steps); the single-thread oracle sets the length at N = 1M
+            ans_d = OracleAnswers(ids_d, pos_d, vel_d, area, prec, 120 if n <= N_STRONG else 60)
             pd = parity_check(ctx, params, ids_d, pos_d, vel_d, prec, "cells", ans_d)
             cm["with_rebuilds"]["parity"] = pd
             if not pd["ok"]:
