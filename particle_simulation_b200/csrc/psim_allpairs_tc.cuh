@@ -115,20 +115,16 @@ __device__ __forceinline__ void umma_commit(unsigned mbar) {
 }
 
 
-// The exact path: one queued candidate j of row ig in the working precision, with the reference's own
-// arithmetic (pair_force, psim_common.cuh).
+// The exact path: one queued candidate j (its record pj already loaded) of row ig in the working precision,
+// with the reference's own arithmetic (pair_force, psim_common.cuh); pair_force's verdict r < r_cut is the
+// predicate of count_pairs_kernel (psim_allpairs.cuh), so it also feeds the audit counter.
 template <class R>
-__device__ __noinline__ void exact_pair(const Real4<R>* __restrict__ pos, const Consts<R>& c, int64_t ig, const Real4<R>& pi,
-                                        int64_t jg, R* f, unsigned* in_range) {
-  if (jg == ig) return;
-  const Real4<R> pj = pos[jg];
-  if (pj.w >= c.huge) return;
+__device__ __forceinline__ void exact_pair(const Consts<R>& c, int64_t ig, const Real4<R>& pi, int64_t jg, const Real4<R>& pj,
+                                           R* f, unsigned* in_range) {
+  if (jg == ig || pj.w >= c.huge) return;
   const R dx = r_sub(pi.x, pj.x), dy = r_sub(pi.y, pj.y), dz = r_sub(pi.z, pj.z);
   const R r2 = r_add(r_add(r_mul(dx, dx), r_mul(dy, dy)), r_mul(dz, dz));
-  if (r2 < c.cut2_pad) {
-    pair_force(pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, c, f[0], f[1], f[2]);
-    if (r_sqrt(r2) < c.r_cut) ++*in_range;         // the predicate of count_pairs_kernel (psim_allpairs.cuh)
-  }
+  if (r2 < c.cut2_pad && pair_force(pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, c, f[0], f[1], f[2])) ++*in_range;
 }
 
 // the queue is addressed in the shared window (one register instead of a generic pointer's two)
@@ -313,13 +309,27 @@ __device__ __noinline__ void flush_queue(FlushCtx<R>* x, unsigned q, int cnt, in
   const Consts<R>& c = *x->c;
   const int64_t ig = x->ig;
   const Real4<R> pi = pos[ig];
+  // Entries are evaluated in queue order (fixed summation order).  The record of the NEXT candidate is in
+  // flight while the current pair term (a square root and two divisions in the working precision) is
+  // evaluated: this loop is the tail of every block, when the tensor pipe is already idle.
+  auto first_j = [&](unsigned v) { return (int64_t)(k_begin + (int)((v >> 6) & 511u)) * (2 * N2) + x->col0 + (int64_t)((v & DENSE) ? 0u : (v & 63u)); };
+  unsigned v = q_load(q, 0);
+  int64_t jg = first_j(v);
+  Real4<R> pj = pos[jg];
   for (int e = 0; e < cnt; ++e) {
-    const unsigned v = q_load(q, e);
-    const int64_t j0 = (int64_t)(k_begin + (int)((v >> 6) & 511u)) * (2 * N2) + x->col0;
-    if (v & DENSE) {
-      for (int u = 0; u < 64; ++u) exact_pair(pos, c, ig, pi, j0 + u, x->f, &x->in_range);
+    const unsigned vc = v;
+    const int64_t jc = jg;
+    Real4<R> pc = pj;
+    if (e + 1 < cnt) { v = q_load(q, e + 1); jg = first_j(v); pj = pos[jg]; }
+    if (vc & DENSE) {                              // all 64 columns of the chunk
+      for (int u = 0; u < 64; ++u) {
+        Real4<R> pn = pc;
+        if (u + 1 < 64) pn = pos[jc + u + 1];
+        exact_pair(c, ig, pi, jc + u, pc, x->f, &x->in_range);
+        pc = pn;
+      }
     } else {
-      exact_pair(pos, c, ig, pi, j0 + (int64_t)(v & 63u), x->f, &x->in_range);
+      exact_pair(c, ig, pi, jc, pc, x->f, &x->in_range);
     }
   }
 }
