@@ -41,3 +41,30 @@ def merge_owned(parts, bounds, n: int):
         out[lo:hi] = a[lo:hi]
     assert bounds[0][0] == 0 and bounds[-1][1] == n
     return out
+
+
+def slice_pairs_of_rank(disp_norm, active, n: int, rank: int, world: int, slices: int):
+    """What slice_top2_kernel computes on one rank (csrc/psim_integrate.cuh): for every reference slice the two
+    largest displacement norms among the ACTIVE particles of the slice that the rank owns (zeros when it owns
+    none).  Returns an array [slices, 2]."""
+    lo, hi = shard_bounds(n, rank, world)
+    out = np.zeros((slices, 2))
+    for k in range(slices):
+        a, b = reference_slice(n, k, slices)
+        a, b = max(a, lo), min(b, hi)
+        if b > a:
+            v = np.sort(disp_norm[a:b][active[a:b].astype(bool)])[::-1]
+            out[k, :min(2, len(v))] = v[:2]
+    return out
+
+
+def merged_trigger(pairs_by_rank, tolerance: float) -> bool:
+    """What housekeeping_kernel decides (csrc/psim_cells.cuh): per slice, the two largest values among all ranks'
+    pairs; the rebuild fires when any slice's two largest sum to more than the tolerance
+    (module_stoermer_verlet_method.f08:168-185 per thread slice, program_...:71,86,92)."""
+    pairs = np.asarray(pairs_by_rank)                       # [world, slices, 2]
+    for k in range(pairs.shape[1]):
+        v = np.sort(pairs[:, k, :].ravel())[::-1]
+        if v[0] + v[1] > tolerance:
+            return True
+    return False

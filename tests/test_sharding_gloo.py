@@ -64,3 +64,53 @@ def test_two_rank_merge_over_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert res == [(0, True, True, 2.0), (1, True, True, 2.0)]
+
+
+def _trigger_worker(rank, world, port, n, slices, seed, q):
+    import torch
+    import torch.distributed as dist
+    from particle_simulation_b200 import sharding as S
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(seed)                   # every rank holds the same displacements, as on the GPUs
+        verdicts = []
+        for trial in range(40):
+            disp = rng.uniform(0.0, 0.2, n)
+            movers = rng.choice(n, 2, replace=False)
+            disp[movers] = rng.uniform(0.2, 0.4, 2)         # two large ones: same slice or not decides the verdict
+            active = (rng.uniform(size=n) > 0.1).astype(np.uint8)
+            mine = torch.from_numpy(S.slice_pairs_of_rank(disp, active, n, rank, world, slices))
+            parts = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(parts, mine)                    # the 2 x slices values per rank of the step's NCCL group
+            got = S.merged_trigger(np.stack([p.numpy() for p in parts]), 0.5)
+            # the reference: each thread slice on its own (single process, all particles)
+            want = False
+            for k in range(slices):
+                a, b = S.reference_slice(n, k, slices)
+                v = np.sort(disp[a:b][active[a:b].astype(bool)])[::-1]
+                want = want or (len(v) >= 2 and v[0] + v[1] > 0.5)
+            verdicts.append((got, want))
+        q.put((rank, all(g == w for g, w in verdicts), sum(w for _, w in verdicts)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("slices", [1, 3])
+def test_per_slice_rebuild_trigger_merged_over_two_ranks(slices):
+    """The reference evaluates its rebuild trigger per NB_OF_THREADS slice; a slice may span ranks.  Per-rank
+    per-slice top-2 pairs, all-gathered and merged slice by slice, must give the reference's verdict."""
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_trigger_worker, args=(r, 2, port, 2000, slices, 17, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in res)
+    fired = res[0][2]
+    assert 0 < fired < 40, "test lost its point: the verdict should vary between trials (%d of 40 fired)" % fired
