@@ -66,3 +66,17 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp")):
                 src = open(os.path.join(base, f), errors="ignore").read()
                 assert not bad.search(src), os.path.join(base, f) + " uses the oracle"
+
+
+def test_fortran_interface_source_binds_every_entry_point(psim):
+    """fortran/psim_binding.f08 cannot be compiled on this project's machines (no Fortran compiler), but it can
+    be kept complete: every symbol include/psim.h declares has a bind(C, name=...) interface in it, and the two
+    interoperable structs have the C structs' field counts."""
+    import os
+    import re
+    src = open(os.path.join(os.path.dirname(psim.__file__), "fortran", "psim_binding.f08")).read()
+    bound = set(re.findall(r'name="(psim_\w+)"', src))
+    assert set(psim.native.EXPORTS) <= bound, sorted(set(psim.native.EXPORTS) - bound)
+    counters = re.search(r"type, bind\(C\) :: psim_counters(.*?)end type psim_counters", src, re.S).group(1)
+    fields = [f for line in counters.strip().splitlines() for f in line.split("::")[1].split(",")]
+    assert len(fields) == len(psim.native.Counters._fields_)
