@@ -21,7 +21,7 @@
 // smallest pieces and of the result.  Inactive and padding records get a row that can never pass (+60000);
 // a particle so far outside the box that S^2 |y|^2 would overflow FP16 (it left the box and the next rebuild
 // will deactivate it) gets a row that ALWAYS passes (-60000): every pair that passes is decided and evaluated
-// exactly, in the working precision, by the exact path (exact_pair -> pair_force, psim_common.cuh), so the
+// exactly, in the working precision, by the exact path (pair_term: pair_force's arithmetic, psim_common.cuh), so the
 // forces are unchanged; the kernel counts the in-range pairs it evaluated for the tests' audit.
 //
 // Organisation (one block of 21 warps per SM, four 128-column FP16 accumulators in TMEM):
@@ -29,10 +29,12 @@
 //   * the TMA producer streams 32 KB (eight tiles) per bulk copy through a 2-slot ring;
 //   * MMA warp w issues the tiles t = w (mod 4) into accumulator w: one instruction and one commit per tile,
 //     one b_full wait per two tiles (the B slot is handed back by a consumer lane, not by a second commit);
-//   * consumer warps split by tile parity: eight warps (4 lane quadrants x 2 column halves) take the even
-//     tiles, eight the odd ones; a warp reads its 32 rows x 64 columns with one tcgen05.ld.32x32b.x32.pack::16b,
-//     releases the accumulator at once and only then ORs the 32 packed registers (16 LOP3): any sign bit set =
-//     a candidate; rare hits go to the 16-bit queue.
+//   * consumer warps: four groups of four (one warp per TMEM lane quadrant); group g serves accumulator g alone,
+//     i.e. the tiles t = g (mod 4).  A warp reads its 32 rows x 128 columns with two
+//     tcgen05.ld.32x32b.x32.pack::16b, releases the accumulator at once and only then ORs the 64 packed
+//     registers (32 LOP3): any sign bit set = a candidate; rare hits go to the 16-bit queue.  (Four warps per
+//     tile instead of eight: an accumulator waits for four releases, and no warp alternates between two
+//     accumulators — tools/microbench/tc_rtt.cu measures 140 against 205 cycles per tile for the two layouts.)
 //   * j-split: when a launch has too few i-blocks to fill the SMs evenly (a shard of a multi-GPU run, a small N)
 //     the j range is cut into S segments, one block each; the partial forces of an i-block meet in global scratch
 //     and the block that arrives last adds them in segment order (fixed order: run-to-run identical results) and
@@ -47,6 +49,10 @@
 namespace psim {
 namespace tc {
 
+#ifndef PSIM_TC_FLUSH_U
+#define PSIM_TC_FLUSH_U 1       // candidates evaluated side by side in the exact path
+#endif
+
 constexpr int MAX_JSPLIT = 8;                   // j segments per i-block (launch-time choice)
 
 
@@ -56,18 +62,18 @@ constexpr int N2 = 128;                         // j records per tile = accumula
 constexpr int NBUF = 4;                         // TMEM ring: four accumulators of 128 columns
 constexpr int NCTL = NBUF;                      // MMA warps
 constexpr int TILE_BYTES = N2 * K * 2;          // 4 KB
-constexpr int TPS = 8;                          // tiles per ring slot (one 32 KB bulk copy)
+constexpr int TPS = 8;                          // tiles per ring slot (one 32 KB bulk copy); a multiple of NBUF
 constexpr int NSLOT = 2;
 constexpr int SLOT_BYTES = TPS * TILE_BYTES;
 constexpr int RING_BYTES = NSLOT * SLOT_BYTES;  // 64 KB
-constexpr int CW = 16;                          // consumer warps: (tile parity) x (4 lane quadrants) x (2 column halves)
+constexpr int CW = 16;                          // consumer warps: (accumulator) x (4 lane quadrants)
 constexpr int TW = 32 * (CW + NCTL + 1);
 constexpr int QC = 64, QPHYS = QC + 64;         // queue: logical capacity + one chunk's unbounded first pass (64 columns)
 constexpr int QMAX_TILE = 5;
 constexpr int QSTRIDE = 32 * CW;
-constexpr int SEG = 512;                        // own tiles per consume call: a queue entry holds a 9-bit tile offset
+constexpr int SEG = 256;                        // own tiles per consume call: a queue entry holds a 9-bit chunk offset (two chunks per tile)
 constexpr int SMEM_BYTES = RING_BYTES + QPHYS * QSTRIDE * 2;   // 64 KB + 128 KB
-constexpr unsigned DENSE = 0x8000u;             // queue entry: [dense:1][own tile - k_begin:9][column:6]
+constexpr unsigned DENSE = 0x8000u;             // queue entry: [dense:1][chunk of 64 columns since k_begin:9][column:6]
 constexpr float BIG = 60000.0f;                 // fits FP16; larger than any S^2 |y|^2 the scaling admits
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -114,18 +120,6 @@ __device__ __forceinline__ void umma_commit(unsigned mbar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(mbar) : "memory");
 }
 
-
-// The exact path: one queued candidate j (its record pj already loaded) of row ig in the working precision,
-// with the reference's own arithmetic (pair_force, psim_common.cuh); pair_force's verdict r < r_cut is the
-// predicate of count_pairs_kernel (psim_allpairs.cuh), so it also feeds the audit counter.
-template <class R>
-__device__ __forceinline__ void exact_pair(const Consts<R>& c, int64_t ig, const Real4<R>& pi, int64_t jg, const Real4<R>& pj,
-                                           R* f, unsigned* in_range) {
-  if (jg == ig || pj.w >= c.huge) return;
-  const R dx = r_sub(pi.x, pj.x), dy = r_sub(pi.y, pj.y), dz = r_sub(pi.z, pj.z);
-  const R r2 = r_add(r_add(r_mul(dx, dx), r_mul(dy, dy)), r_mul(dz, dz));
-  if (r2 < c.cut2_pad && pair_force(pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, c, f[0], f[1], f[2])) ++*in_range;
-}
 
 // the queue is addressed in the shared window (one register instead of a generic pointer's two)
 __device__ __forceinline__ void q_store(unsigned qaddr, int e, unsigned v) {
@@ -249,10 +243,19 @@ constexpr unsigned SIGNS = 0x80008000u;
 
 // -DPSIM_TC_PROF: clock64 timeline of block 0 (tiles 0..511), printed at the end of the kernel.
 // events: 0..3 per MMA warp: [4 w + 0] b_full/d_empty seen, [4 w + 1] issued + committed;
-//         16 + 3 * consumer warp + {0: d_full seen, 1: load complete, 2: accumulator released}
+//         16 + 5 * consumer warp + {0: d_full seen, 1: load complete, 2: accumulator released, 3: slot bookkeeping done,
+//                                   4: reduction done}
 #ifdef PSIM_TC_PROF
-__device__ long long g_trace[16 + 3 * CW][512];
+__device__ long long g_trace[16 + 5 * CW][512];
+#ifndef PSIM_TC_PROF_BLOCK
+#define PSIM_TC_PROF_BLOCK 1000
+#endif
+__device__ long long g_flush[CW][10];   // per consumer warp of block PSIM_TC_PROF_BLOCK: start; per call: consume returned, flush done, entries
+#ifdef PSIM_TC_PROF_LIGHT                  // only the per-block stamps (g_flush): the tile loop runs undisturbed
+#define TR(ev, tile) {}
+#else
 #define TR(ev, tile) { if (blockIdx.x == 0 && (tile) < 512) g_trace[ev][tile] = clock64(); }
+#endif
 #else
 #define TR(ev, tile) {}
 #endif
@@ -294,101 +297,169 @@ __device__ __forceinline__ void queue_chunk(const unsigned (&r)[32], unsigned tc
   }
 }
 
+
+// What the exact path needs of Consts, and the exact path's state: ONE 128-byte line of local memory per thread.
+// (The consumer loop is a function of its own with 64 accumulator registers live, so its caller can keep next to
+// nothing in registers across the call; behind a pointer to the kernel's parameter copy the exact path started
+// every call with a chain of three local-memory misses, ~4,000 cycles during which the tensor pipeline stood.)
 template <class R>
-struct FlushCtx {
-  const Real4<R>* pos; const Consts<R>* c; int64_t ig;
-  int64_t col0;              // global index of column 0 of this thread's chunk in ITS first tile of the block's j segment
+struct PairConsts { R r_cut, cut2_pad, huge, r_min, F_rcut, epsilon; };
+template <class R>
+struct __align__(128) FlushCtx {
+  const Real4<R>* pos; int64_t ig;
+  int64_t col0;              // global index of column 0 of this thread's FIRST own tile in the block's j segment
   R f[3]; unsigned in_range;
+  PairConsts<R> c;
 };
 
-// k_begin: the own-tile index that queue codes are relative to; own tile k is tile 2 k + parity of the segment.
+// The exact path: one queued candidate j (its record pj already loaded) of row ig in the working precision, with
+// the reference's own arithmetic — pair_force (psim_common.cuh) without branches: (ax, ay, az) = 0 - the pair's
+// force term (bit-identical to what pair_force subtracts) when the pair is in range, 0 otherwise.  Returns the
+// verdict r < r_cut, the predicate of count_pairs_kernel (psim_allpairs.cuh): it feeds the audit counter.
+template <class R>
+__device__ __forceinline__ bool pair_term(const PairConsts<R>& c, int64_t ig, const Real4<R>& pi, int64_t jg, const Real4<R>& pj,
+                                          R& ax, R& ay, R& az) {
+  const R dx = r_sub(pi.x, pj.x), dy = r_sub(pi.y, pj.y), dz = r_sub(pi.z, pj.z);       // stoermer:117
+  const R r2 = r_add(r_add(r_mul(dx, dx), r_mul(dy, dy)), r_mul(dz, dz));
+  const R r = r_sqrt(r2);                                                               // :119
+  const bool in = (jg != ig) & !(pj.w >= c.huge) & (r2 < c.cut2_pad) & (r < c.r_cut);   // :121
+  const R rs = in ? r : (R)1;                          // keeps the unused evaluations finite
+  const R q = r_div(c.r_min, rs);
+  const R q2 = r_mul(q, q);
+  const R s = r_mul(r_mul(q2, q2), q2);                                                 // :123
+  const R F = r_mul(r_div(s, r_mul(rs, rs)), r_sub((R)1, s));                           // :124
+  const R g = r_sub(F, c.F_rcut);
+  const R k12 = (R)12;
+  ax = in ? r_sub((R)0, r_mul(r_mul(r_mul(dx, k12), c.epsilon), g)) : (R)0;             // :126, :128
+  ay = in ? r_sub((R)0, r_mul(r_mul(r_mul(dy, k12), c.epsilon), g)) : (R)0;
+  az = in ? r_sub((R)0, r_mul(r_mul(r_mul(dz, k12), c.epsilon), g)) : (R)0;
+  return in;
+}
+
+// k_begin: the own-tile index that queue codes are relative to; own tile k is tile 4 k + group of the segment,
+// chunk c since k_begin = columns 64 (c & 1) ... of own tile k_begin + (c >> 1).
+// Entries are evaluated U at a time and added in queue order (fixed summation order).  U = 1 measured best on
+// B200 (f64: 3.01 ms per step at N = 262,144 against 3.11 with U = 2 and 3.17 with U = 3): the exact path is a
+// chain of ~45 dependent FP64 operations per candidate (~1,000 cycles), and while it runs the warp's accumulator
+// and, through the ring, the tensor pipeline wait: ~6 % of a block's time (tools/tc_timeline.py, -DPSIM_TC_PROF_LIGHT).
 template <class R>
 __device__ __noinline__ void flush_queue(FlushCtx<R>* x, unsigned q, int cnt, int k_begin) {
   if (cnt == 0) return;
+  constexpr int U = PSIM_TC_FLUSH_U;
   const Real4<R>* __restrict__ pos = x->pos;
-  const Consts<R>& c = *x->c;
-  const int64_t ig = x->ig;
+  const PairConsts<R> c = x->c;
+  const int64_t ig = x->ig, col0 = x->col0;
   const Real4<R> pi = pos[ig];
-  // Entries are evaluated in queue order (fixed summation order).  The record of the NEXT candidate is in
-  // flight while the current pair term (a square root and two divisions in the working precision) is
-  // evaluated: this loop is the tail of every block, when the tensor pipe is already idle.
-  auto first_j = [&](unsigned v) { return (int64_t)(k_begin + (int)((v >> 6) & 511u)) * (2 * N2) + x->col0 + (int64_t)((v & DENSE) ? 0u : (v & 63u)); };
-  unsigned v = q_load(q, 0);
-  int64_t jg = first_j(v);
-  Real4<R> pj = pos[jg];
-  for (int e = 0; e < cnt; ++e) {
-    const unsigned vc = v;
-    const int64_t jc = jg;
-    Real4<R> pc = pj;
-    if (e + 1 < cnt) { v = q_load(q, e + 1); jg = first_j(v); pj = pos[jg]; }
-    if (vc & DENSE) {                              // all 64 columns of the chunk
-      for (int u = 0; u < 64; ++u) {
-        Real4<R> pn = pc;
-        if (u + 1 < 64) pn = pos[jc + u + 1];
-        exact_pair(c, ig, pi, jc + u, pc, x->f, &x->in_range);
-        pc = pn;
+  auto first_j = [&](unsigned v) {
+    const int ch = (int)((v >> 6) & 511u);
+    return (int64_t)(k_begin + (ch >> 1)) * (NBUF * N2) + col0 + (int64_t)((ch & 1) * 64) + (int64_t)((v & DENSE) ? 0u : (v & 63u));
+  };
+  R f0 = x->f[0], f1 = x->f[1], f2 = x->f[2];
+  unsigned in_range = x->in_range;
+  for (int e = 0; e < cnt; e += U) {
+    unsigned v[U]; int64_t jg[U]; Real4<R> pj[U];
+    unsigned dense = 0u;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const bool ok = e + u < cnt;
+      v[u] = ok ? q_load(q, e + u) : 0u;
+      jg[u] = ok ? first_j(v[u]) : ig;
+      dense |= v[u] & DENSE;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) pj[u] = pos[jg[u]];
+    if (dense) {                                   // rare: a chunk with more than QMAX_TILE candidates in one row
+      R fd[3] = {f0, f1, f2};
+#pragma unroll                                     // static indices: v, jg, pj must stay in registers
+      for (int u = 0; u < U; ++u) {
+        if (e + u >= cnt) continue;
+        if (v[u] & DENSE) {                        // all 64 columns of the chunk
+          Real4<R> pc = pj[u];
+#pragma unroll 1
+          for (int w = 0; w < 64; ++w) {
+            Real4<R> pn = pc;
+            if (w + 1 < 64) pn = pos[jg[u] + w + 1];
+            R ax, ay, az;
+            in_range += pair_term(c, ig, pi, jg[u] + w, pc, ax, ay, az) ? 1u : 0u;
+            fd[0] = r_add(fd[0], ax); fd[1] = r_add(fd[1], ay); fd[2] = r_add(fd[2], az);
+            pc = pn;
+          }
+        } else {
+          R ax, ay, az;
+          in_range += pair_term(c, ig, pi, jg[u], pj[u], ax, ay, az) ? 1u : 0u;
+          fd[0] = r_add(fd[0], ax); fd[1] = r_add(fd[1], ay); fd[2] = r_add(fd[2], az);
+        }
       }
+      f0 = fd[0]; f1 = fd[1]; f2 = fd[2];
     } else {
-      exact_pair(c, ig, pi, jc, pc, x->f, &x->in_range);
+      R ax[U], ay[U], az[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) in_range += pair_term(c, ig, pi, jg[u], pj[u], ax[u], ay[u], az[u]) ? 1u : 0u;
+#pragma unroll
+      for (int u = 0; u < U; ++u) { f0 = r_add(f0, ax[u]); f1 = r_add(f1, ay[u]); f2 = r_add(f2, az[u]); }
     }
   }
+  x->f[0] = f0; x->f[1] = f1; x->f[2] = f2; x->in_range = in_range;
 }
 
 // The consumer tile loop of one warp (a function of its own, so that the exact path's double-precision
-// register needs stay out of it; loop state in uniform registers — see consume_tiles in psim_allpairs_tc.cuh).
-// The warp owns the tiles of one parity: own tile k is tile 2 k + p and lives in accumulator p + 2 (k & 1),
-// phase k >> 1.  Groups of four own tiles start at multiples of four, so the phase parities are immediates
-// (0, 0, 1, 1).  Per tile: wait for the accumulator, load the warp's 32 rows x 64 columns, HAND THE ACCUMULATOR
-// BACK, then reduce from registers.  What bounds this kernel is the round trip of an accumulator (consumers'
-// release -> MMA warp wakes -> issue -> tensor pipe -> commit -> consumers wake -> load; ~1000 cycles measured
-// with the reduction inside it, tools/tc_timeline.py): 512 TMEM columns per round trip is all the tensor pipe
-// gets, so the release comes as early as the data allows and the reduction of tile k overlaps the MMA side
-// of the next round instead of delaying it.
-// lane_base addresses the warp's 64 columns of accumulator p; accumulator p + 2 is 256 columns further.
-// dbar: shared address of d_full[p]; d_full[p + 2] is 16 bytes further, d_empty[b] 8 * NBUF bytes after
-// d_full[b].  releases_slots: this warp hands the ring slot of its tiles back to the TMA producer: lane 0
-// arrives on b_empty[(t / TPS) % NSLOT] once per own tile after the tile's d_full wait (the MMA that read the
-// B tile is complete then); bempty0 = shared address of b_empty[0].
-// ntk (own tiles): multiple of 4.  Returns (next own tile << 32) | queue length; queue codes are relative to
-// k_begin.  Returns at the end, every SEG own tiles, and when some lane's queue could overflow in the next group.
-__device__ __noinline__ unsigned long long consume_tiles(unsigned q, unsigned lane_base, unsigned dbar, unsigned bempty0,
-                                                           int releases_slots, int ntk_v, int k_begin_v) {
+// register needs stay out of it; loop state in uniform registers).
+// The warp's group g owns accumulator g: own tile k is tile 4 k + g, phase k & 1 of the accumulator's barriers.
+// Per tile: wait for the accumulator, load the warp's 32 rows x 128 columns, HAND THE ACCUMULATOR BACK, then
+// reduce from registers.  What bounds this kernel is the round trip of an accumulator (consumers' release ->
+// MMA warp wakes -> issue -> tensor pipe -> commit -> consumers wake -> load; tools/microbench/tc_rtt.cu):
+// 512 TMEM columns per round trip is all the tensor pipe gets, so the release comes as early as the data
+// allows and the reduction of tile k overlaps the MMA side of the next round instead of delaying it.
+// lane_base addresses the warp's rows of accumulator g.  dfull / dempty: shared addresses of the accumulator's
+// two barriers.  releases_slots: this warp hands the ring slot of its tiles back to the TMA producer: lane 0
+// arrives on b_empty[(t / TPS) % NSLOT] once per own tile, together with the accumulator's release (the MMA
+// that read the B tile is complete then); bempty0 = shared address of b_empty[0].
+// ntk (own tiles): multiple of 2.  Returns (next own tile << 32) | queue length; queue codes are relative to
+// k_begin.  Returns at the end, every SEG own tiles, and when some lane's queue could overflow in the next pair.
+__device__ __noinline__ unsigned long long consume_tiles(unsigned q, unsigned lane_base, unsigned dfull, unsigned dempty,
+                                                           unsigned bempty0, int releases_slots, int ntk_v, int k_begin_v) {
   const int lane = threadIdx.x & 31;
   const int k_begin = (int)__reduce_max_sync(0xffffffffu, (unsigned)k_begin_v);
   const int ntk = (int)__reduce_max_sync(0xffffffffu, (unsigned)ntk_v);
   const bool release_slot = __reduce_max_sync(0xffffffffu, (unsigned)releases_slots) != 0u;   // uniform
-  // own tile k = tile 2 k + p: its ring slot is ((2 k + p) / TPS) % NSLOT = (k / 4) % NSLOT for TPS = 8
-#define PSIM_TC_ORDER asm volatile("" : "+r"(r[0]), "+r"(r[9]), "+r"(r[18]), "+r"(r[27]));
-#define PSIM_TC_TILE(which, par_, kk, code)                                                    \
+  // own tile k = tile 4 k + g: its ring slot is ((4 k + g) / TPS) % NSLOT = (k / 2) % NSLOT for TPS = 8
+#define PSIM_TC_TRT(kk) (4 * (kk) + (int)(threadIdx.x >> 7))
+#define PSIM_TC_TILE(par_, kk, code)                                                           \
   {                                                                                              \
-    mbar_wait_warp(dbar + 16u * (which), (par_));   /* all lanes leave together: .aligned load next */ \
-    if (lane == 0) TR(16 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
+    mbar_wait_warp(dfull, (par_));                  /* all lanes leave together: .aligned load next */ \
+    if (lane == 0) TR(16 + 5 * (int)(threadIdx.x >> 5), PSIM_TC_TRT(kk))                         \
     asm volatile("tcgen05.fence::after_thread_sync;");                                           \
-    PSIM_TMEM_LD32_PACK16(r, lane_base + (unsigned)((which) * 2 * N2));                          \
-    if (release_slot && lane == 0) mbar_arrive(bempty0 + 8u * (unsigned)(((kk) >> 2) % NSLOT)); \
+    PSIM_TMEM_LD32_PACK16(ra, lane_base);                                                        \
+    PSIM_TMEM_LD32_PACK16(rb, lane_base + 64u);                                                  \
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");                                 \
-    if (lane == 0) TR(17 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
+    if (lane == 0) TR(17 + 5 * (int)(threadIdx.x >> 5), PSIM_TC_TRT(kk))                         \
     asm volatile("tcgen05.fence::before_thread_sync;");   /* values are in registers */          \
     __syncwarp();                                                                                \
-    if (lane == 0) mbar_arrive(dbar + 8u * NBUF + 16u * (which));                            \
-    if (lane == 0) TR(18 + 3 * (int)(threadIdx.x >> 5), 2 * (kk) + ((int)(threadIdx.x >> 7) >> 1))   \
-    /* the reduction may not be scheduled ahead of the release: its first operands pass through here */ \
-    PSIM_TC_ORDER                                                                              \
-    queue_chunk(r, (code), q, cnt);                                                            \
+    /* A real branch: ptxas schedules within basic blocks; as predicated code the release ended up */ \
+    /* behind half of the reduction, and the reduction's first half between the two loads. */     \
+    if (lane == 0) {                                                                             \
+      mbar_arrive(dempty);                                                                       \
+      TR(18 + 5 * (int)(threadIdx.x >> 5), PSIM_TC_TRT(kk))                                      \
+      if (release_slot) mbar_arrive(bempty0 + 8u * (unsigned)(((kk) / (TPS / NBUF)) % NSLOT));   \
+      TR(19 + 5 * (int)(threadIdx.x >> 5), PSIM_TC_TRT(kk))                                      \
+    }                                                                                            \
+    __syncwarp();                                                                                \
+    queue_chunk(ra, (code), q, cnt);                                                             \
+    queue_chunk(rb, (code) + 64u, q, cnt);                                                       \
+    if (lane == 0) TR(20 + 5 * (int)(threadIdx.x >> 5), PSIM_TC_TRT(kk))                         \
   }
-  unsigned r[32];
+  unsigned ra[32], rb[32];
   int cnt = 0, k0 = k_begin;
   for (;;) {
-    const unsigned tc0 = (unsigned)(k0 - k_begin) << 6;
-    PSIM_TC_TILE(0, 0u, k0, tc0)
-    PSIM_TC_TILE(1, 0u, k0 + 1, tc0 + 64u)
-    PSIM_TC_TILE(0, 1u, k0 + 2, tc0 + 128u)
-    PSIM_TC_TILE(1, 1u, k0 + 3, tc0 + 192u)
-    k0 += 4;
-    // the next group adds at most 4 QMAX_TILE logical entries
+    const unsigned tc0 = (unsigned)(k0 - k_begin) << 7;
+    PSIM_TC_TILE(0u, k0, tc0)
+    PSIM_TC_TILE(1u, k0 + 1, tc0 + 128u)
+    k0 += 2;
+    // the next pair of tiles adds at most 4 QMAX_TILE logical entries
     if (k0 >= ntk || k0 - k_begin >= SEG || __any_sync(0xffffffffu, cnt > QC - 4 * QMAX_TILE)) break;
   }
 #undef PSIM_TC_TILE
+#undef PSIM_TC_TRT
   return ((unsigned long long)(unsigned)k0 << 32) | (unsigned)cnt;
 }
 
@@ -409,8 +480,7 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool consumer = warp < CW;
   const int row = (warp & 3) * 32 + lane;          // accumulator row = TMEM lane (consumers)
-  const int grp = (warp >> 2) & 3;                 // consumers: tile parity (grp >> 1) and column half (grp & 1)
-  const int par = grp >> 1, half64 = grp & 1;
+  const int grp = (warp >> 2) & 3;                 // consumers: the accumulator this warp's group serves
   const int S = js.S;
   const int ib = (int)blockIdx.x / S, seg = (int)blockIdx.x - ib * S;
   const int64_t ig = a.i_lo + (int64_t)ib * M + row;
@@ -429,7 +499,7 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
   }
   if (tid == 0) {
     for (int s = 0; s < NSLOT; ++s) { mbar_init(smem_u32(&b_full[s]), 1); mbar_init(smem_u32(&b_empty[s]), TPS); }
-    for (int b = 0; b < NBUF; ++b) { mbar_init(smem_u32(&d_full[b]), 1); mbar_init(smem_u32(&d_empty[b]), CW / 2); }
+    for (int b = 0; b < NBUF; ++b) { mbar_init(smem_u32(&d_full[b]), 1); mbar_init(smem_u32(&d_empty[b]), CW / NBUF); }
     asm volatile("fence.mbarrier_init.release.cluster;");
   }
   if (warp == CW) {
@@ -443,17 +513,19 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
   const unsigned tm = tmem_base_s;
 
   FlushCtx<R> fx;
-  fx.pos = a.pos_cur; fx.c = &c; fx.ig = ig; fx.col0 = (int64_t)(t_lo + par) * N2 + half64 * 64;
+  fx.pos = a.pos_cur; fx.ig = ig; fx.col0 = (int64_t)(t_lo + grp) * N2;
   fx.f[0] = fx.f[1] = fx.f[2] = (R)0; fx.in_range = 0;
+  fx.c.r_cut = c.r_cut; fx.c.cut2_pad = c.cut2_pad; fx.c.huge = c.huge; fx.c.r_min = c.r_min; fx.c.F_rcut = c.F_rcut;
+  fx.c.epsilon = c.epsilon;
   if (warp == CW + NCTL) {
     if (lane == 0) {
-      // ===== TMA producer: one 32 KB bulk copy per eight tiles (this GPU's memory), as far ahead as the ring allows =====
+      // ===== TMA producer: one bulk copy per ring slot (this GPU's memory), as far ahead as the ring allows =====
       const int nq = nt / TPS;
       const unsigned bfull0 = smem_u32(&b_full[0]), bempty0 = smem_u32(&b_empty[0]), sB0 = smem_u32(sB);
       const unsigned char* src = bops + (size_t)t_lo * TILE_BYTES;
       for (int Q = 0; Q < nq; ++Q) {
         const int s = Q % NSLOT;
-        mbar_wait(bempty0 + 8u * s, (unsigned)(((Q / NSLOT) & 1) ^ 1));   // all eight tiles of the slot multiplied (fresh: passes)
+        mbar_wait(bempty0 + 8u * s, (unsigned)(((Q / NSLOT) & 1) ^ 1));   // all tiles of the slot multiplied (fresh: passes)
         mbar_expect_tx(bfull0 + 8u * s, SLOT_BYTES);
         bulk_copy_g2s(sB0 + (unsigned)(s * SLOT_BYTES), src + (size_t)Q * SLOT_BYTES, SLOT_BYTES, bfull0 + 8u * s);
       }
@@ -470,13 +542,14 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
       const unsigned dfull = smem_u32(&d_full[w]), dempty = smem_u32(&d_empty[w]);
       const unsigned bfull0 = smem_u32(&b_full[0]), sB0 = smem_u32(sB);
       for (int k = 0; k < ntw; ++k) {
-        const int Q = k >> 1, s = Q % NSLOT;       // tile t = w + 4 k sits in ring fill Q = t / 8, at position w + 4 (k & 1)
-        if ((k & 1) == 0) mbar_wait(bfull0 + 8u * s, (unsigned)((Q / NSLOT) & 1));      // the slot's eight tiles landed
+        constexpr int KPS = TPS / NCTL;            // own tiles per fill
+        const int Q = k / KPS, s = Q % NSLOT;      // tile t = w + 4 k sits in ring fill Q = t / TPS, at position w + 4 (k % KPS)
+        if (k % KPS == 0) mbar_wait(bfull0 + 8u * s, (unsigned)((Q / NSLOT) & 1));      // the slot's tiles landed
         TR(4 * w + 2, w + 4 * k)
         mbar_wait(dempty, (unsigned)((k & 1) ^ 1));                                     // accumulator drained
         TR(4 * w + 0, w + 4 * k)
         asm volatile("tcgen05.fence::after_thread_sync;");
-        const unsigned long long db = make_desc(sB0 + (unsigned)(s * SLOT_BYTES + (w + 4 * (k & 1)) * TILE_BYTES));
+        const unsigned long long db = make_desc(sB0 + (unsigned)(s * SLOT_BYTES + (w + 4 * (k % KPS)) * TILE_BYTES));
         asm volatile(
             "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
@@ -488,15 +561,27 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
   } else {
     // ===== consumers =====
     const unsigned q = smem_u32(sB + RING_BYTES) + 2u * (unsigned)tid;
-    const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(par * N2 + half64 * 64);
-    const unsigned dbar = smem_u32(&d_bar[par]);
+    const unsigned lane_base = tm + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)(grp * N2);
+    const unsigned dfull = smem_u32(&d_full[grp]), dempty = smem_u32(&d_empty[grp]);
     const unsigned bempty0 = smem_u32(&b_empty[0]);
-    const int releases = ((warp & 3) == 0 && half64 == 0) ? 1 : 0;     // one warp per tile parity hands the ring slots back
-    const int ntk = nt / 2;
+    const int releases = (warp & 3) == 0 ? 1 : 0;     // one warp per group hands the ring slots back (TPS arrivals per slot)
+    const int ntk = nt / NBUF;
     int k = 0;
+#ifdef PSIM_TC_PROF
+    int call = 0;
+    const bool prof_block = blockIdx.x == PSIM_TC_PROF_BLOCK && lane == 0;
+    if (prof_block) g_flush[warp][0] = clock64();
+#endif
     while (k < ntk) {
-      const unsigned long long r = consume_tiles(q, lane_base, dbar, bempty0, releases, ntk, k);
+      const unsigned long long r = consume_tiles(q, lane_base, dfull, dempty, bempty0, releases, ntk, k);
+#ifdef PSIM_TC_PROF
+      if (prof_block && call < 3) { g_flush[warp][1 + 3 * call] = clock64(); g_flush[warp][3 + 3 * call] = (long long)(unsigned)r; }
+#endif
       flush_queue<R>(&fx, q, (int)(unsigned)r, k);
+#ifdef PSIM_TC_PROF
+      if (prof_block && call < 3) g_flush[warp][2 + 3 * call] = clock64();
+      ++call;
+#endif
       k = (int)(r >> 32);
     }
     unsigned in_range = fx.in_range;
@@ -548,13 +633,20 @@ allpairs_tc_kernel(const StepArgs<R> a, const unsigned char* __restrict__ bops, 
   }
 #ifdef PSIM_TC_PROF
   __syncthreads();
+  if (blockIdx.x == PSIM_TC_PROF_BLOCK && tid == 0) {
+    const long long z = g_flush[0][0], e = clock64();
+    for (int w = 0; w < CW; ++w)
+      printf("FL w%d: start %lld | returned %lld flushed %lld entries %lld | returned %lld flushed %lld entries %lld | block end %lld\n", w,
+             g_flush[w][0] - z, g_flush[w][1] - z, g_flush[w][2] - z, g_flush[w][3], g_flush[w][4] - z, g_flush[w][5] - z, g_flush[w][6], e - z);
+  }
   if (blockIdx.x == 0 && tid == 0) {
     const long long z = g_trace[2][256];
     for (int t = 256; t < 268; ++t) {
-      const int w = t & 3, p = t & 1;
+      const int w = t & 3;
       printf("TR t=%d mma: b_full %lld d_empty %lld committed %lld |", t, g_trace[4 * w + 2][t] - z, g_trace[4 * w][t] - z, g_trace[4 * w + 1][t] - z);
-      for (int cw = 8 * p; cw < 8 * p + 8; ++cw)
-        printf(" w%d: %lld %lld %lld", cw, g_trace[16 + 3 * cw][t] - z, g_trace[17 + 3 * cw][t] - z, g_trace[18 + 3 * cw][t] - z);
+      for (int cw = 4 * w; cw < 4 * w + 4; ++cw)
+        printf(" w%d: %lld %lld %lld %lld %lld", cw, g_trace[16 + 5 * cw][t] - z, g_trace[17 + 5 * cw][t] - z, g_trace[18 + 5 * cw][t] - z,
+               g_trace[19 + 5 * cw][t] - z, g_trace[20 + 5 * cw][t] - z);
       printf("\n");
     }
   }
