@@ -145,7 +145,8 @@ __global__ void __launch_bounds__(512) ld_rate_kernel(long long* cycles, unsigne
 }
 
 // ---------------------------------------------------------------- C. reduction instruction rates
-// OP 0: FMNMX3, 1: VHMNMX (half2 three-input min), 2: LOP3 (a | b | c), 3: HMNMX2 (two-input)
+// OP 0: FMNMX3, 1: VHMNMX (half2 three-input min), 2: LOP3 (a | b | c), 3: HMNMX2 (two-input), 4: HSETP2 chain,
+// 5: HFMA2 (the FMA pipe, for reference), 6: four HSETP2 beside four LOP3 (do the two pipes overlap?)
 template <int OP>
 __global__ void __launch_bounds__(512) alu_rate_kernel(long long* cycles, unsigned* sink, const unsigned* seed, int iters) {
   unsigned v[8], s1 = seed[threadIdx.x & 31], s2 = seed[32 + (threadIdx.x & 31)];
@@ -162,6 +163,29 @@ __global__ void __launch_bounds__(512) alu_rate_kernel(long long* cycles, unsign
       if (OP == 2) asm volatile("lop3.b32 %0, %0, %1, %2, 0xFE;" : "+r"(v[k]) : "r"(nb), "r"(s1));
       if (OP == 3) { __half2 a = *reinterpret_cast<__half2*>(&v[k]), b = *reinterpret_cast<__half2*>(&nb);
                      a = __hmin2(a, b); v[k] = *reinterpret_cast<unsigned*>(&a); }
+      if (OP == 5) asm volatile("fma.rn.f16x2 %0, %0, %1, %2;" : "+r"(v[k]) : "r"(nb), "r"(s1));
+    }
+    if (OP == 4 || OP == 6) {
+      // 8 (OP 4) or 4 (OP 6, beside 4 LOP3) packed-half compares "any entry negative", chained through a predicate
+      unsigned any;
+      if (OP == 4)
+        asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %9, 0;\n\t"
+                     "setp.lt.or.f16x2 p|q, %1, %10, p;\n\tsetp.lt.or.f16x2 p|q, %2, %10, p;\n\t"
+                     "setp.lt.or.f16x2 p|q, %3, %10, p;\n\tsetp.lt.or.f16x2 p|q, %4, %10, p;\n\t"
+                     "setp.lt.or.f16x2 p|q, %5, %10, p;\n\tsetp.lt.or.f16x2 p|q, %6, %10, p;\n\t"
+                     "setp.lt.or.f16x2 p|q, %7, %10, p;\n\tsetp.lt.or.f16x2 p|q, %8, %10, p;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(any) : "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(s2 & 1u), "r"(0u));
+      else
+        asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %9, 0;\n\t"
+                     "setp.lt.or.f16x2 p|q, %1, %10, p;\n\tlop3.b32 %5, %5, %6, %11, 0xFE;\n\t"
+                     "setp.lt.or.f16x2 p|q, %2, %10, p;\n\tlop3.b32 %6, %6, %7, %11, 0xFE;\n\t"
+                     "setp.lt.or.f16x2 p|q, %3, %10, p;\n\tlop3.b32 %7, %7, %8, %11, 0xFE;\n\t"
+                     "setp.lt.or.f16x2 p|q, %4, %10, p;\n\tlop3.b32 %8, %8, %5, %11, 0xFE;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(any), "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7])
+                     : "r"(s2 & 1u), "r"(0u), "r"(s1));
+      v[0] ^= any;
     }
     s1 += s2;                                         // keeps the loop from collapsing
   }
@@ -353,13 +377,17 @@ int main() {
   {
     std::vector<unsigned> seed(64); for (auto& s : seed) s = 0x3c003c00u + (rand() & 0x03ff03ff);
     unsigned* dseed; CK(cudaMalloc(&dseed, 256)); CK(cudaMemcpy(dseed, seed.data(), 256, cudaMemcpyHostToDevice));
-    const char* names[4] = {"FMNMX3 (min.f32 x3)", "VHMNMX (min.f16x2 x3)", "LOP3 (a|b|c)", "HMNMX2 (min.f16x2 x2)"};
-    for (int op = 0; op < 4; ++op) {
+    const char* names[7] = {"FMNMX3 (min.f32 x3)", "VHMNMX (min.f16x2 x3)", "LOP3 (a|b|c)", "HMNMX2 (min.f16x2 x2)",
+                            "HSETP2 (lt.or.f16x2) x8", "HFMA2 (fma.f16x2)", "4 HSETP2 + 4 LOP3"};
+    for (int op = 0; op < 7; ++op) {
       const int iters = 4000; float ms = 0; long long cyc = 0; cudaError_t e = cudaSuccess;
       if (op == 0) e = timed([&] { alu_rate_kernel<0><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
       if (op == 1) e = timed([&] { alu_rate_kernel<1><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
       if (op == 2) e = timed([&] { alu_rate_kernel<2><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
       if (op == 3) e = timed([&] { alu_rate_kernel<3><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
+      if (op == 4) e = timed([&] { alu_rate_kernel<4><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
+      if (op == 5) e = timed([&] { alu_rate_kernel<5><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
+      if (op == 6) e = timed([&] { alu_rate_kernel<6><<<nsm, 512>>>(dcyc, dsink, dseed, iters); }, &ms, &cyc);
       const double winstr = (double)iters * 8 * 16;                        // warp instructions per SM (+ ~3 of loop overhead per 8)
       printf("  %-22s %s, %lld cycles: %.2f warp-instr/clk/SM = %.2f per SMSP (reciprocal %.2f clk)\n", names[op], cudaGetErrorString(e), cyc,
              winstr / cyc, winstr / cyc / 4, 4 * cyc / winstr);
