@@ -196,9 +196,9 @@ def test_conservation_and_energy(psim, oracle, algo):
 
 
 @pytest.mark.parametrize("precision", [4, 8])
-@pytest.mark.parametrize("case", ["lattice_65536", "hot_gas_32768", "two_cubes", "corner_of_big_box"])
+@pytest.mark.parametrize("case", ["lattice_65536", "hot_gas_32768", "two_cubes", "corner_of_big_box", "dense_row_chunks"])
 def test_tensor_core_filter_drops_no_pair(psim, oracle, precision, case):
-    """The tensor-core distance filter (split-TF32 Gram matrix) must be conservative: the ordered in-range
+    """The tensor-core distance filter (split-FP16 Gram matrix) must be conservative: the ordered in-range
     pairs its exact path evaluated (psim_counters.filter_pairs) equal the exact O(N^2) count, and stay equal
     while the configuration moves; the forces equal the CPU oracle's brute-force evaluation at the same
     positions.  corner_of_big_box puts the block in the far corner of the 198 x 198 x 99 box of the
@@ -214,6 +214,19 @@ def test_tensor_core_filter_drops_no_pair(psim, oracle, precision, case):
     elif case == "corner_of_big_box":
         ids, pos, vel = G.lattice_block((32, 32, 16), (177.0, 177.0, 88.0), thermal=0.1, seed=5)
         kw = dict(length_of_area=(198.0, 198.0, 99.0))
+    elif case == "dense_row_chunks":
+        # a compressed block (radius 0.85: ~75 neighbours in range) whose lattice order puts 7 to 9 of a row's
+        # neighbours into 64 consecutive indices: the kernel's queue turns such a chunk into ONE "dense" entry and
+        # its exact path walks all 64 columns (a branch the other cases never take); a shuffled copy of the same
+        # block spreads the neighbours over all chunks instead (sparse entries, long queues, mid-block flushes)
+        ids, pos, vel = G.lattice_block((16, 16, 16), (49.5, 49.5, 49.5), radius=0.85, seed=3)
+        rng = np.random.default_rng(17)
+        pos = pos + rng.uniform(-0.02, 0.02, pos.shape)
+        perm = rng.permutation(len(ids))
+        ids = np.concatenate([ids, ids + len(ids)]).astype(np.int32)
+        pos = np.concatenate([pos, pos[perm] + np.array([30.0, 0.0, 0.0])])
+        vel = np.concatenate([vel, vel[perm]]) * 0.0
+        kw = dict(delta_t=1e-7)
     else:   # strongly perturbed lattice: many pairs close to the cut-off on both sides
         ids, pos, vel, area = G.synthetic(32768, thermal=0.1)
         rng = np.random.default_rng(11)
