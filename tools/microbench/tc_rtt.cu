@@ -71,6 +71,7 @@ template <int NB, int NT, int CW, int CPT, int NMMA, int REDUCE, int PROBE, int 
 __global__ void __launch_bounds__(32 * (CW + NMMA), 1)
 rtt_kernel(long long* cycles, unsigned* sink, int ntiles, long long* lat) {
   constexpr int G = CW / CPT, PARTS = CPT / 4, WIDTH = NT / PARTS;
+  constexpr unsigned TCOLS = NB * NT <= 32 ? 32u : NB * NT <= 64 ? 64u : NB * NT <= 128 ? 128u : NB * NT <= 256 ? 256u : 512u;
   static_assert(NB * NT <= 512 && NB % G == 0 && NB % NMMA == 0 && (WIDTH == 64 || WIDTH == 128), "configuration");
   __shared__ __align__(128) unsigned char sA[M * 32];
   __shared__ __align__(128) unsigned char sB[NT * 32];
@@ -85,7 +86,7 @@ rtt_kernel(long long* cycles, unsigned* sink, int ntiles, long long* lat) {
     asm volatile("fence.mbarrier_init.release.cluster;");
   }
   if (warp == CW) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(&tmem_base)));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&tmem_base)), "r"(TCOLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -166,7 +167,7 @@ rtt_kernel(long long* cycles, unsigned* sink, int ntiles, long long* lat) {
   if (PROBE == 2 && blockIdx.x == 0 && tid == CW * 32) { lat[0] = s_wake; lat[1] = s_issue; lat[2] = s_seen; }
   if (warp == CW) {
     __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tm));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tm), "r"(TCOLS));
   }
 }
 
@@ -271,8 +272,10 @@ self_issue_kernel(long long* cycles, unsigned* sink, int ntiles) {
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); return 2; } } while (0)
 
 template <int NB, int NT, int CW, int CPT, int NMMA, int REDUCE, int PROBE, int WAIT = 0>
-static int run(const char* name, int nsm, long long* dcyc, unsigned* dsink, long long* dlat) {
+static int run(const char* name, int nsm, long long* dcyc, unsigned* dsink, long long* dlat, int per_sm = 1) {
   const int ntiles = 4096;
+  const int nsm_real = nsm;
+  nsm *= per_sm;                      // per_sm blocks share an SM (each with its own part of TMEM)
   CK(cudaMemset(dlat, 0, 64));
   rtt_kernel<NB, NT, CW, CPT, NMMA, REDUCE, PROBE, WAIT><<<nsm, 32 * (CW + NMMA)>>>(dcyc, dsink, ntiles, dlat);   // warm-up
   rtt_kernel<NB, NT, CW, CPT, NMMA, REDUCE, PROBE, WAIT><<<nsm, 32 * (CW + NMMA)>>>(dcyc, dsink, ntiles, dlat);
@@ -282,9 +285,10 @@ static int run(const char* name, int nsm, long long* dcyc, unsigned* dsink, long
   CK(cudaMemcpy(lat, dlat, 64, cudaMemcpyDeviceToHost));
   double mean = 0; long long mx = 0;
   for (long long c : cyc) { mean += (double)c / nsm; mx = c > mx ? c : mx; }
-  const double per_tile = mean / ntiles, per_128 = per_tile * 128.0 / NT;
+  (void)nsm_real;
+  const double per_tile = mean / ntiles / per_sm, per_128 = per_tile * 128.0 / NT;
   printf("  %-44s %8.1f cycles per tile of %3d columns = %6.1f per 128 x 128 pair tests (max SM %.1f)\n", name, per_tile, NT,
-         per_128, (double)mx / ntiles * 128.0 / NT);
+         per_128, (double)mx / ntiles / per_sm * 128.0 / NT);
   if (PROBE == 2)
     printf("      issuing thread 0 (block 0, mean cycles per own tile): in the d_empty wait %.0f, fence + MMA %.0f, commit %.0f\n",
            (double)lat[0] * NMMA / ntiles, (double)lat[1] * NMMA / ntiles, (double)lat[2] * NMMA / ntiles);
@@ -313,7 +317,7 @@ int main() {
   cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0));
   const int nsm = p.multiProcessorCount;
   long long *dcyc, *dlat; unsigned* dsink;
-  CK(cudaMalloc(&dcyc, nsm * sizeof(long long))); CK(cudaMalloc(&dlat, 64)); CK(cudaMalloc(&dsink, (size_t)nsm * 1024 * 4));
+  CK(cudaMalloc(&dcyc, 2 * nsm * sizeof(long long))); CK(cudaMalloc(&dlat, 64)); CK(cudaMalloc(&dsink, (size_t)2 * nsm * 1024 * 4));
   int rc = 0;
   printf("SMs %d\n\n== E. one accumulator: the round trip itself (no other work on the SM) ==\n", nsm);
   //        NB   NT  CW CPT NMMA RED PROBE
@@ -340,6 +344,12 @@ int main() {
   rc |= run<4, 128, 16,  4,  1,  1,  2>("4 x 128, 16 warps, 4/tile, 1 issuer", nsm, dcyc, dsink, dlat);
   rc |= run<4, 128, 16,  4,  2,  1,  2>("4 x 128, 16 warps, 4/tile, 2 issuers", nsm, dcyc, dsink, dlat);
   rc |= run<4, 128, 16,  8,  4,  1,  2>("4 x 128, 16 warps, 8/tile, 4 issuers", nsm, dcyc, dsink, dlat);
+  printf("\n== J. two blocks per SM, each with half of TMEM (cycles per tile per SM) ==\n");
+  rc |= run<2, 128,  8,  4,  2,  1,  0>("2 blocks x (2 x 128, 8 warps, 4/tile, 2 issuers)", nsm, dcyc, dsink, dlat, 2);
+  rc |= run<2, 128,  8,  4,  2,  0,  0>("  same, no reduction", nsm, dcyc, dsink, dlat, 2);
+  rc |= run<2, 128,  8,  4,  2,  1,  0>("1 block  x (2 x 128, 8 warps, 4/tile, 2 issuers)", nsm, dcyc, dsink, dlat, 1);
+  rc |= run<4,  64,  8,  4,  4,  1,  0>("2 blocks x (4 x 64, 8 warps, 4/tile, 4 issuers)", nsm, dcyc, dsink, dlat, 2);
+  rc |= run<2, 128, 16,  8,  2,  1,  0>("2 blocks x (2 x 128, 16 warps, 8/tile, 2 issuers)", nsm, dcyc, dsink, dlat, 2);
   printf("\n== I. the consumers issue the next MMA themselves (4 x 128, 16 warps, 4/tile) ==\n");
   rc |= run_self<1, 0, 0>("two x32 loads, first warp issues", nsm, dcyc, dsink);
   rc |= run_self<1, 1, 0>("one x64 load, first warp issues", nsm, dcyc, dsink);
