@@ -109,6 +109,10 @@ typedef struct psim_counters {
                              * (owned i) x (n - 1) for an all-pairs kernel; for the cell-binned path the tests its
                              * 27-cell neighbourhoods needed, counted only while PSIM_OPT_KERNEL_TIMING is on
                              * (-1 otherwise).  bench.py's roofline accounting uses it. */
+  int64_t peer_push_steps;  /* sharded handles: steps whose positions reached the other ranks as peer-memory stores
+                             * from inside the fused force kernel (NVLink) instead of an NCCL all-gather; 0 when the
+                             * ranks could not map each other's buffers (CUDA IPC), with PSIM_GATHER=nccl in the
+                             * environment, and on single-GPU handles */
 } psim_counters;
 
 typedef struct psim_sim psim_sim;   /* opaque */

@@ -23,6 +23,17 @@
 
 namespace psim {
 
+// Sharded runs, fused step: where the drift of an owned particle is stored besides this GPU's own buffer — the
+// same record of every other rank's copy of the buffer (peer memory over NVLink, plain stores).  The all-gather of
+// the position shards thereby happens inside the force kernel, block by block, and overlaps its arithmetic; what is
+// left of the collective is a flag per rank (publish_kernel / await_kernel, psim_integrate.cuh).  world == 0: off.
+constexpr int MAX_PEERS = 16;
+template <class R>
+struct PeerPush {
+  int world, rank;
+  Real4<R>* pos_nxt[MAX_PEERS];   // [r]: rank r's copy of the buffer this step writes (entry `rank` is not used)
+};
+
 template <class R>
 struct StepArgs {
   const Real4<R>* pos_cur;   // x_n, all particles           [n_pad]
@@ -37,7 +48,23 @@ struct StepArgs {
   int64_t n_pad;             // multiple of the j-tile
   int64_t i_lo, i_hi;        // owned slice of i (multi-GPU shard); i_hi <= n
   Consts<R> c;
+  PeerPush<R> peers;         // MODE_FORCE_KICK_DRIFT only
 };
+
+// x_{n+1} of owned particle i: this GPU's buffer and every peer's.
+template <class R>
+__device__ __forceinline__ void store_next(const StepArgs<R>& a, int64_t i, const Real4<R>& x) {
+  a.pos_nxt[i] = x;
+  if (a.peers.world > 1) {
+    for (int r = 0; r < a.peers.world; ++r)
+      if (r != a.peers.rank) a.peers.pos_nxt[r][i] = x;
+    // The stores must have arrived before the flag that publish_kernel raises after this kernel: a thread's
+    // system-scope fence covers its own stores, and the block's ticket (block_top2_store) and the kernel boundary
+    // carry the order on.  Without it a record could land in the peer's buffer after the peer had already
+    // deactivated it (seen: cell path, particles leaving the box, active flags differing on one rank).
+    __threadfence_system();
+  }
+}
 
 enum { MODE_FORCE = 0, MODE_FORCE_KICK = 1, MODE_FORCE_KICK_DRIFT = 2 };
 
@@ -110,7 +137,7 @@ __device__ __forceinline__ void step_epilogue(const StepArgs<R>& a, int64_t i, R
   const Consts<R>& c = a.c;
   const Real4<R> p = a.pos_cur[i];
   if (p.w >= c.huge) {                       // inactive: carried along untouched
-    if (MODE == MODE_FORCE_KICK_DRIFT) a.pos_nxt[i] = p;
+    if (MODE == MODE_FORCE_KICK_DRIFT) store_next(a, i, p);
     return;
   }
   Real4<R> fn; fn.x = fx; fn.y = fy; fn.z = fz; fn.w = (R)0;
@@ -126,7 +153,7 @@ __device__ __forceinline__ void step_epilogue(const StepArgs<R>& a, int64_t i, R
   Real4<R> d = a.disp[i], xn;
   const R dr = drift_one(c, p, v, fn.x, fn.y, fn.z, d, xn);
   a.disp[i] = d;
-  a.pos_nxt[i] = xn;
+  store_next(a, i, xn);
   top2_push(first, second, dr);
 }
 

@@ -208,6 +208,18 @@ class SimT final : public psim_sim {
                 cudaEvent_t ready = nullptr, done = nullptr; bool used = false; };
   Slot slots[PSIM_FRAME_SLOTS];
   ncclComm_t comm = nullptr;
+  // Peer stores (PeerPush, psim_allpairs.cuh): every rank's position buffers, trigger table and flag array, mapped
+  // through CUDA IPC at create; the fused force kernel then stores x_{n+1} of its particles into all of them and
+  // the per-step all-gather shrinks to publish_kernel + await_kernel.  Off (NCCL all-gather every step) when any
+  // rank could not map its peers, with PSIM_GATHER=nccl, and for the unfused drift.
+  bool peer_push = false;
+  Real4<R>* peer_pos[2][MAX_PEERS] = {};
+  R* peer_top2[MAX_PEERS] = {};
+  unsigned long long* peer_flags[MAX_PEERS] = {};
+  unsigned long long* flags = nullptr;   // [world] this rank's flags, written by the peers
+  unsigned long long epoch = 0;          // steps exchanged by peer stores so far (the same on every rank)
+  int64_t peer_push_steps = 0;
+  std::vector<void*> ipc_opened;
 
   ~SimT() override { destroy(); }
 
@@ -215,7 +227,10 @@ class SimT final : public psim_sim {
     if (device >= 0) cudaSetDevice(device);
     if (stream) cudaStreamSynchronize(stream);
     if (side) cudaStreamSynchronize(side);
+    for (void* p : ipc_opened) cudaIpcCloseMemHandle(p);
+    ipc_opened.clear(); peer_push = false;
     if (comm) { g_nccl.CommDestroy(comm); comm = nullptr; }
+    cudaFree(flags); flags = nullptr;
     cells.destroy();
     for (auto& s : slots) {
       cudaFree(s.d_pos); cudaFree(s.d_vel); cudaFree(s.d_act);
@@ -306,6 +321,8 @@ class SimT final : public psim_sim {
       ncclUniqueId nid;
       std::memcpy(&nid, uid, sizeof nid);
       PSIM_NCCL(g_nccl.CommInitRank(&comm, world, nid, rank));
+      psim_status st = map_peers();
+      if (st != PSIM_OK) return st;
     }
     // velocities, then positions + initial activation + initial forces
     if (vel_h) PSIM_CK(cudaMemcpyAsync(tmp3, vel_h, sizeof(R) * 3 * n, cudaMemcpyHostToDevice, stream));
@@ -337,6 +354,65 @@ class SimT final : public psim_sim {
     return PSIM_OK;
   }
 
+  // Exchange CUDA IPC handles of the shared arrays over the communicator and map every peer's.  Collective.  Any
+  // rank that cannot (same process, no peer access, PSIM_GATHER=nccl) makes ALL ranks keep the NCCL all-gather.
+  psim_status map_peers() {
+    struct Handles { cudaIpcMemHandle_t pos0, pos1, top2, flags; int ok; int pad[15]; };
+    static_assert(sizeof(Handles) == 4 * 64 + 64, "handle record");
+    PSIM_CK(cudaMalloc(&flags, sizeof(unsigned long long) * MAX_PEERS));
+    PSIM_CK(cudaMemsetAsync(flags, 0, sizeof(unsigned long long) * MAX_PEERS, stream));
+    Handles mine;
+    std::memset(&mine, 0, sizeof mine);
+    const char* env = std::getenv("PSIM_GATHER");
+    mine.ok = world <= MAX_PEERS && !(env && std::strcmp(env, "nccl") == 0);
+    if (mine.ok) {
+      mine.ok = cudaIpcGetMemHandle(&mine.pos0, pos[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.pos1, pos[1]) == cudaSuccess &&
+                cudaIpcGetMemHandle(&mine.top2, top2_rank) == cudaSuccess && cudaIpcGetMemHandle(&mine.flags, flags) == cudaSuccess;
+      cudaGetLastError();
+    }
+    unsigned char* d_all = nullptr;
+    PSIM_CK(cudaMalloc(&d_all, sizeof(Handles) * world));
+    std::vector<Handles> all(world);
+    auto exchange = [&]() -> psim_status {
+      PSIM_CK(cudaMemcpyAsync(d_all + sizeof(Handles) * rank, &mine, sizeof mine, cudaMemcpyHostToDevice, stream));
+      PSIM_NCCL(g_nccl.AllGather(d_all + sizeof(Handles) * rank, d_all, sizeof(Handles), ncclUint8, comm, stream));
+      PSIM_CK(cudaMemcpyAsync(all.data(), d_all, sizeof(Handles) * world, cudaMemcpyDeviceToHost, stream));
+      PSIM_CK(cudaStreamSynchronize(stream));
+      return PSIM_OK;
+    };
+    psim_status st = exchange();
+    if (st != PSIM_OK) { cudaFree(d_all); return st; }
+    bool ok = true;
+    for (int r = 0; r < world; ++r) ok = ok && all[r].ok;
+    if (ok) {
+      for (int r = 0; r < world && ok; ++r) {
+        if (r == rank) { peer_pos[0][r] = pos[0]; peer_pos[1][r] = pos[1]; peer_top2[r] = top2_rank; peer_flags[r] = flags; continue; }
+        void* q[4] = {nullptr, nullptr, nullptr, nullptr};
+        const cudaIpcMemHandle_t* hs[4] = {&all[r].pos0, &all[r].pos1, &all[r].top2, &all[r].flags};
+        for (int k = 0; k < 4 && ok; ++k) {
+          ok = cudaIpcOpenMemHandle(&q[k], *hs[k], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+          if (ok) ipc_opened.push_back(q[k]);
+        }
+        cudaGetLastError();
+        peer_pos[0][r] = (Real4<R>*)q[0]; peer_pos[1][r] = (Real4<R>*)q[1];
+        peer_top2[r] = (R*)q[2]; peer_flags[r] = (unsigned long long*)q[3];
+      }
+    }
+    // second round: did every rank map every peer?
+    mine.ok = ok ? 1 : 0;
+    st = exchange();
+    cudaFree(d_all);
+    if (st != PSIM_OK) return st;
+    for (int r = 0; r < world; ++r) ok = ok && all[r].ok;
+    if (!ok) {
+      for (void* p : ipc_opened) cudaIpcCloseMemHandle(p);
+      ipc_opened.clear();
+      cudaGetLastError();
+    }
+    peer_push = ok;
+    return PSIM_OK;
+  }
+
   StepArgs<R> step_args() const {
     StepArgs<R> a;
     a.pos_cur = pos[cur]; a.pos_nxt = pos[cur ^ 1];
@@ -346,6 +422,11 @@ class SimT final : public psim_sim {
     a.ticket = &ctrl->ticket;
     a.n_pad = n_pad; a.i_lo = i_lo; a.i_hi = i_hi;
     a.c = c;
+    a.peers.world = 0; a.peers.rank = rank;
+    if (peer_push && fused) {            // only MODE_FORCE_KICK_DRIFT kernels store x_{n+1}
+      a.peers.world = world;
+      for (int r = 0; r < world; ++r) a.peers.pos_nxt[r] = peer_pos[cur ^ 1][r];
+    }
     return a;
   }
 
@@ -533,6 +614,8 @@ class SimT final : public psim_sim {
     h.n = n; h.i_lo = i_lo; h.i_hi = i_hi; h.c = c;
     h.cells = (algo == PSIM_FORCE_CELL_BINNED && cells.allocated()) ? 1 : 0;
     h.force_rebin = force_rebin ? 1 : 0;
+    // a rank without particles never builds the cell tables, yet must keep its copies of the inactive records
+    h.carry_all = (algo == PSIM_FORCE_CELL_BINNED && !h.cells && peer_push) ? 1 : 0;
     if (h.cells) cells.fill_args(h);
     const int grid = (int)std::min<int64_t>(house_grid_max, std::max<int64_t>(2, blocks(n, 256)));
     void* args[] = {&h};
@@ -543,7 +626,8 @@ class SimT final : public psim_sim {
   }
 
   // After x_{n+1} of the owned slice is in pos[cur^1]: exchange (sharded), then housekeeping, swap.
-  psim_status finish_drift() {
+  // pushed: the drift came from a fused force kernel that stored x_{n+1} into the peers' buffers as well
+  psim_status finish_drift(bool pushed = false) {
     Real4<R>* nxt = pos[cur ^ 1];
     const int ns = c.slices;
     R* mine = top2_rank + 2 * ns * rank;
@@ -554,7 +638,15 @@ class SimT final : public psim_sim {
       slice_top2_kernel<R><<<ns, 256, 0, stream>>>(nxt, disp, n, i_lo, i_hi, mine, c);
       ++launches;
     }
-    if (world > 1) {
+    if (world > 1 && pushed) {
+      ++epoch; ++peer_push_steps;
+      PeerMail<R> m;
+      m.world = world; m.rank = rank; m.nvals = 2 * ns; m.mine = mine;
+      for (int r = 0; r < world; ++r) { m.top2[r] = peer_top2[r]; m.flags[r] = peer_flags[r]; }
+      publish_kernel<R><<<1, 64, 0, stream>>>(m, epoch);
+      await_kernel<<<1, 32, 0, stream>>>(flags, world, rank, epoch, ctrl, 5000000000ull);
+      launches += 2;
+    } else if (world > 1) {
       PSIM_NCCL(g_nccl.GroupStart());
       PSIM_NCCL(g_nccl.AllGather(nxt + shard * rank, nxt, (size_t)shard * 4, NcclType<R>::v, comm, stream));
       PSIM_NCCL(g_nccl.AllGather(mine, top2_rank, (size_t)2 * ns, NcclType<R>::v, comm, stream));
@@ -580,8 +672,11 @@ class SimT final : public psim_sim {
           ++launches;
         }
       }
+      // the previous trip of THIS call ran a fused kernel (whether or not this rank owns particles): every rank
+      // takes the same branch
+      const bool pushed = peer_push && can_fuse && s > 0;
       pending_drift = false;
-      psim_status st = finish_drift();
+      psim_status st = finish_drift(pushed);
       if (st != PSIM_OK) return st;
       const bool last = (s == nsteps - 1);
       if (can_fuse) {
@@ -682,12 +777,14 @@ class SimT final : public psim_sim {
       PSIM_CK(cudaStreamSynchronize(stream));
       out->filter_tests = (int64_t)ft;
     }
+    if (h.comm_timeout) { g_last_error = "a peer's positions did not arrive within 5 s (peer-store gather)"; return PSIM_ERR_COMM; }
     out->steps = steps;
     out->rebuilds = (int64_t)h.rebuilds;
     out->kernel_launches = launches + cells.launches;
     out->force_launches = force_launches;
     out->force_ms = force_ms;
     out->force_timed = force_timed;
+    out->peer_push_steps = peer_push_steps;
     out->n_active = (int64_t)h.n_active;
     return PSIM_OK;
   }

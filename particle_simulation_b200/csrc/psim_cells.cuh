@@ -214,6 +214,7 @@ struct HouseArgs {
   Consts<R> c;
   // cell path (cells == 0: all-pairs, nothing to bin)
   int cells, force_rebin, ncell;
+  int carry_all;          // no cell tables on this rank (it owns nothing): still carry every inactive record over
   int32_t *key, *perm, *cell_start, *own_start, *cell_of, *own_slots;
   unsigned *count, *own_count, *fill;
   Real4<R>* posj;
@@ -353,8 +354,16 @@ housekeeping_kernel(const HouseArgs<R> h) {
   }
 
   if (h.cells) {
-    for (int64_t k = gtid; k < h.n; k += gsz) h.posj[k] = h.pos_new[h.perm[k]];
-    for (int64_t i = h.i_lo + gtid; i < h.i_hi; i += gsz) {
+    // (every inactive record, not only the owned ones: when positions travel by peer stores no all-gather
+    // spreads a rank's copies, and every rank knows all of them anyway)
+    for (int64_t k = gtid; k < h.n; k += gsz) {
+      const int32_t i = h.perm[k];
+      const Real4<R> p = h.pos_new[i];
+      h.posj[k] = p;
+      if (p.w >= c.huge) h.pos_other[i] = p;
+    }
+  } else if (h.carry_all) {
+    for (int64_t i = gtid; i < h.n; i += gsz) {
       const Real4<R> p = h.pos_new[i];
       if (p.w >= c.huge) h.pos_other[i] = p;
     }

@@ -55,7 +55,7 @@ module psim_binding
   type, bind(C) :: psim_counters
     integer(c_int64_t) :: steps, rebuilds, kernel_launches, force_launches
     real(c_double)     :: force_ms
-    integer(c_int64_t) :: force_timed, n_active, filter_pairs, filter_tests
+    integer(c_int64_t) :: force_timed, n_active, filter_pairs, filter_tests, peer_push_steps
   end type psim_counters
 
   interface

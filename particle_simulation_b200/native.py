@@ -55,6 +55,7 @@ class Counters(C.Structure):
         ("n_active", C.c_int64),
         ("filter_pairs", C.c_int64),
         ("filter_tests", C.c_int64),
+        ("peer_push_steps", C.c_int64),
     ]
 
 

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol(psim):
 def test_params_struct_layout_matches_header(psim, oracle):
     import ctypes as C
     assert C.sizeof(psim.native.Params) == 5 * 8 + 2 * 3 * 8 + 2 * 4 == C.sizeof(oracle.Params)
-    assert C.sizeof(psim.native.Counters) == 9 * 8
+    assert C.sizeof(psim.native.Counters) == 10 * 8
 
 
 def test_no_device_is_a_loud_error_not_a_cpu_fallback(psim):

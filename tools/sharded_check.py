@@ -105,10 +105,15 @@ def main():
         if scenario == "lattice_65536":
             good = good and rebuilds >= 1
         if rank == 0:
-            print("%s algo=%s f%d scenario=%s NB_OF_THREADS=%d ranks=%d: rebuilds %d (oracle %d), inactive %d, dx=%.3g dv=%.3g" % (
+            print("%s algo=%s f%d scenario=%s NB_OF_THREADS=%d ranks=%d: rebuilds %d (oracle %d), inactive %d, dx=%.3g dv=%.3g, "
+                  "%d of %d steps gathered by peer stores" % (
                 "ok      " if good else "MISMATCH", algo, 8 * precision, scenario, threads, world, rebuilds, o.rebuilds,
-                int((ar == 0).sum()), dx, dv), flush=True)
-        elif not good:
+                int((ar == 0).sum()), dx, dv, sim.counters().peer_push_steps, sum(chunks)), flush=True)
+        if not good and not np.array_equal(a, ar):
+            bad = np.nonzero(a != ar)[0]
+            print("rank %d: active flags differ at particles %s (owned range %d..%d): here %s, oracle %s" % (
+                rank, bad[:8].tolist(), sim.i_lo, sim.i_hi, a[bad[:8]].tolist(), ar[bad[:8]].tolist()), flush=True)
+        if rank != 0 and not good:
             print("rank %d: MISMATCH algo=%s precision=%d scenario=%s threads=%d dx=%g dv=%g rebuilds %d vs %d flags_equal=%s" % (
                 rank, algo, precision, scenario, threads, dx, dv, rebuilds, o.rebuilds, np.array_equal(a, ar)), flush=True)
         ok = ok and good
