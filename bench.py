@@ -408,7 +408,8 @@ def measure_path(ctx, params, ids, pos, vel, prec, kernel, steps, warmup, sample
     rebuilds = int(c1.rebuilds - c0.rebuilds)
     out = {"value": pairs_total * steps / (ms * 1e-3), "unit": "pair-interactions/s", "ms_per_step": ms / steps,
            "timesteps_per_s": steps / (ms * 1e-3), "steps": steps, "gpu_launches": launches,
-           "rebuilds_in_timed_steps": rebuilds, "clocks": clocks}
+           "rebuilds_in_timed_steps": rebuilds, "clocks": clocks,
+           "peer_push_steps": int(c1.peer_push_steps - c0.peer_push_steps)}
 
     # ---- roofline: per-launch duration of the force kernel, events on the library's stream ----
     pin_own = sim.pairs_in_range()
@@ -538,7 +539,12 @@ def main():
         "dtype": "f64" if prec == 8 else "f32", "data": "synthetic",
         "timesteps_per_s": main_m["timesteps_per_s"],
         "config": {"workload": workload_name(n, area), "n_particles": n, "algo": args.algo, "kernel": kernel,
-                   "parallelism": "i-sharded x%d, position all-gather per step" % world if world > 1 else "single GPU",
+                   "parallelism": ("i-sharded x%d; positions reach the other ranks as peer-memory stores from inside the "
+                                   "fused force kernel (NVLink), one flag per rank per step (%d of %d timed steps; the "
+                                   "rest: NCCL all-gather)" % (world, main_m["peer_push_steps"], args.steps)
+                                   if main_m["peer_push_steps"] > 0 else
+                                   "i-sharded x%d, NCCL all-gather of the position shards per step" % world)
+                                  if world > 1 else "single GPU",
                    "sizes": "N=262,144 (BASELINE configs[3]) on 1/2/4 GPUs, N=1,048,576 (configs[4]) on 8; "
                             "strong_n262144 carries the fixed-size line on 8 GPUs",
                    "l2": "not flushed between steps: every step reads the positions the previous step wrote "

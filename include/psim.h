@@ -135,7 +135,13 @@ psim_status psim_create(const psim_params* params, int precision, int64_t n,
  * All ranks pass the full particle arrays.  nccl_unique_id is the 128-byte
  * ncclUniqueId produced by psim_comm_unique_id on rank 0 and distributed by the
  * host (torch.distributed, MPI, a file ...).  Every sharded handle owns its own
- * communicator: use a fresh id per handle. */
+ * communicator: use a fresh id per handle.
+ * When the ranks are processes of one node whose GPUs can address each other, create also maps every rank's
+ * position buffers into the others (CUDA IPC): the fused force kernel then stores x_{n+1} of its particles into
+ * all of them as it finishes each block, and the per-step NCCL all-gather shrinks to one flag per rank
+ * (psim_counters.peer_push_steps counts such steps).  PSIM_GATHER=nccl in the environment keeps the all-gather;
+ * it is also what happens when any rank cannot map a peer.  All ranks must then call psim_advance with the
+ * same step counts, as they must for the collective anyway. */
 psim_status psim_create_sharded(const psim_params* params, int precision, int64_t n,
                                 const int32_t* id, const void* pos, const void* vel,
                                 int device, int rank, int world,
