@@ -218,6 +218,7 @@ class SimT final : public psim_sim {
   unsigned long long* peer_flags[MAX_PEERS] = {};
   unsigned long long* flags = nullptr;   // [world] this rank's flags, written by the peers
   unsigned long long epoch = 0;          // steps exchanged by peer stores so far (the same on every rank)
+  static constexpr unsigned long long kAwaitTimeoutNs = 30000000000ull;   // a peer that silent has died
   int64_t peer_push_steps = 0;
   std::vector<void*> ipc_opened;
 
@@ -644,7 +645,7 @@ class SimT final : public psim_sim {
       m.world = world; m.rank = rank; m.nvals = 2 * ns; m.mine = mine;
       for (int r = 0; r < world; ++r) { m.top2[r] = peer_top2[r]; m.flags[r] = peer_flags[r]; }
       publish_kernel<R><<<1, 64, 0, stream>>>(m, epoch);
-      await_kernel<<<1, 32, 0, stream>>>(flags, world, rank, epoch, ctrl, 5000000000ull);
+      await_kernel<<<1, 32, 0, stream>>>(flags, world, rank, epoch, ctrl, kAwaitTimeoutNs);
       launches += 2;
     } else if (world > 1) {
       PSIM_NCCL(g_nccl.GroupStart());
@@ -720,6 +721,11 @@ class SimT final : public psim_sim {
     PSIM_CK(cudaSetDevice(device));
     PSIM_CK(cudaStreamSynchronize(stream));
     PSIM_CK(cudaStreamSynchronize(side));
+    if (peer_push && peer_push_steps > 0) {          // did every await see its peers?
+      unsigned t = 0;
+      PSIM_CK(cudaMemcpy(&t, &ctrl->comm_timeout, sizeof t, cudaMemcpyDeviceToHost));
+      if (t) { g_last_error = "a peer's positions did not arrive within 30 s (peer-store exchange)"; return PSIM_ERR_COMM; }
+    }
     return PSIM_OK;
   }
 
@@ -777,7 +783,7 @@ class SimT final : public psim_sim {
       PSIM_CK(cudaStreamSynchronize(stream));
       out->filter_tests = (int64_t)ft;
     }
-    if (h.comm_timeout) { g_last_error = "a peer's positions did not arrive within 5 s (peer-store gather)"; return PSIM_ERR_COMM; }
+    if (h.comm_timeout) { g_last_error = "a peer's positions did not arrive within 30 s (peer-store exchange)"; return PSIM_ERR_COMM; }
     out->steps = steps;
     out->rebuilds = (int64_t)h.rebuilds;
     out->kernel_launches = launches + cells.launches;
