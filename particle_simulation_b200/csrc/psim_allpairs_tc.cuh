@@ -39,7 +39,10 @@
 //     the j range is cut into S segments, one block each; the partial forces of an i-block meet in global scratch
 //     and the block that arrives last adds them in segment order (fixed order: run-to-run identical results) and
 //     runs the kick/drift epilogue.
-//   * TMA bulk copies here read this GPU's own memory only (the B rows are rebuilt locally after the all-gather).
+//   * sharded runs: the epilogue stores x_{n+1} into this GPU's buffer and into every peer's (plain stores over
+//     NVLink, PeerPush in psim_allpairs.cuh) — the position exchange rides on the kernel's own blocks;
+//   * TMA bulk copies here read this GPU's own memory only (the B rows are rebuilt locally from the exchanged
+//     positions).
 #pragma once
 
 #include <cuda_fp16.h>
