@@ -315,30 +315,6 @@ struct __align__(128) FlushCtx {
   PairConsts<R> c;
 };
 
-// The exact path: one queued candidate j (its record pj already loaded) of row ig in the working precision, with
-// the reference's own arithmetic — pair_force (psim_common.cuh) without branches: (ax, ay, az) = 0 - the pair's
-// force term (bit-identical to what pair_force subtracts) when the pair is in range, 0 otherwise.  Returns the
-// verdict r < r_cut, the predicate of count_pairs_kernel (psim_allpairs.cuh): it feeds the audit counter.
-template <class R>
-__device__ __forceinline__ bool pair_term(const PairConsts<R>& c, int64_t ig, const Real4<R>& pi, int64_t jg, const Real4<R>& pj,
-                                          R& ax, R& ay, R& az) {
-  const R dx = r_sub(pi.x, pj.x), dy = r_sub(pi.y, pj.y), dz = r_sub(pi.z, pj.z);       // stoermer:117
-  const R r2 = r_add(r_add(r_mul(dx, dx), r_mul(dy, dy)), r_mul(dz, dz));
-  const R r = r_sqrt(r2);                                                               // :119
-  const bool in = (jg != ig) & !(pj.w >= c.huge) & (r2 < c.cut2_pad) & (r < c.r_cut);   // :121
-  const R rs = in ? r : (R)1;                          // keeps the unused evaluations finite
-  const R q = r_div(c.r_min, rs);
-  const R q2 = r_mul(q, q);
-  const R s = r_mul(r_mul(q2, q2), q2);                                                 // :123
-  const R F = r_mul(r_div(s, r_mul(rs, rs)), r_sub((R)1, s));                           // :124
-  const R g = r_sub(F, c.F_rcut);
-  const R k12 = (R)12;
-  ax = in ? r_sub((R)0, r_mul(r_mul(r_mul(dx, k12), c.epsilon), g)) : (R)0;             // :126, :128
-  ay = in ? r_sub((R)0, r_mul(r_mul(r_mul(dy, k12), c.epsilon), g)) : (R)0;
-  az = in ? r_sub((R)0, r_mul(r_mul(r_mul(dz, k12), c.epsilon), g)) : (R)0;
-  return in;
-}
-
 // k_begin: the own-tile index that queue codes are relative to; own tile k is tile 4 k + group of the segment,
 // chunk c since k_begin = columns 64 (c & 1) ... of own tile k_begin + (c >> 1).
 // Entries are evaluated U at a time and added in queue order (fixed summation order).  U = 1 measured best on

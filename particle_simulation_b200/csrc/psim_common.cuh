@@ -106,6 +106,30 @@ __device__ __forceinline__ bool pair_force(R xi, R yi, R zi, R xj, R yj, R zj,
   return true;
 }
 
+// pair_force without branches, for exact paths that evaluate queued candidates (tensor-core kernel, cell kernel):
+// candidate j (its record pj already loaded) of particle ig in the working precision, the reference's own arithmetic: (ax, ay, az) = 0 - the pair's
+// force term (bit-identical to what pair_force subtracts) when the pair is in range, 0 otherwise.  Returns the
+// verdict r < r_cut, the predicate of count_pairs_kernel (psim_allpairs.cuh): it feeds the audit counter.
+template <class R, class CT>
+__device__ __forceinline__ bool pair_term(const CT& c, int64_t ig, const Real4<R>& pi, int64_t jg, const Real4<R>& pj,
+                                          R& ax, R& ay, R& az) {
+  const R dx = r_sub(pi.x, pj.x), dy = r_sub(pi.y, pj.y), dz = r_sub(pi.z, pj.z);       // stoermer:117
+  const R r2 = r_add(r_add(r_mul(dx, dx), r_mul(dy, dy)), r_mul(dz, dz));
+  const R r = r_sqrt(r2);                                                               // :119
+  const bool in = (jg != ig) & !(pj.w >= c.huge) & (r2 < c.cut2_pad) & (r < c.r_cut);   // :121
+  const R rs = in ? r : (R)1;                          // keeps the unused evaluations finite
+  const R q = r_div(c.r_min, rs);
+  const R q2 = r_mul(q, q);
+  const R s = r_mul(r_mul(q2, q2), q2);                                                 // :123
+  const R F = r_mul(r_div(s, r_mul(rs, rs)), r_sub((R)1, s));                           // :124
+  const R g = r_sub(F, c.F_rcut);
+  const R k12 = (R)12;
+  ax = in ? r_sub((R)0, r_mul(r_mul(r_mul(dx, k12), c.epsilon), g)) : (R)0;             // :126, :128
+  ay = in ? r_sub((R)0, r_mul(r_mul(r_mul(dy, k12), c.epsilon), g)) : (R)0;
+  az = in ? r_sub((R)0, r_mul(r_mul(r_mul(dz, k12), c.epsilon), g)) : (R)0;
+  return in;
+}
+
 // (first, second) = the two largest values seen (module_stoermer_verlet_method.f08:168-173)
 template <class R>
 __device__ __forceinline__ void top2_push(R& first, R& second, R v) {
