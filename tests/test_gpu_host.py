@@ -175,13 +175,24 @@ def test_edge_cases(psim, oracle):
     assert e.value.status == 5
 
 
-def test_sharded_run_matches_single_gpu():
-    """Two ranks, NCCL all-gather of the position shards per step (needs 2 GPUs)."""
+@pytest.mark.parametrize("gather", ["peer_stores", "nccl"])
+def test_sharded_run_matches_single_gpu(gather):
+    """Two ranks against the oracle (needs 2 GPUs), with both ways of exchanging the position shards: peer-memory
+    stores from inside the fused force kernel (the default between processes of one node) and the NCCL all-gather
+    (PSIM_GATHER=nccl; also the fallback)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
+    env = dict(os.environ)
+    if gather == "nccl":
+        env["PSIM_GATHER"] = "nccl"
+    else:
+        env.pop("PSIM_GATHER", None)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                        "--master-addr", "127.0.0.1", "--master-port", "29533",
-                        os.path.join(ROOT, "tools", "sharded_check.py")], capture_output=True, text=True, timeout=600)
+                        "--master-addr", "127.0.0.1", "--master-port", "29533" if gather == "nccl" else "29534",
+                        os.path.join(ROOT, "tools", "sharded_check.py")], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "sharded check ok" in r.stdout
+    pushed = "57 of 60 steps gathered by peer stores" in r.stdout
+    if gather == "nccl":
+        assert not pushed, r.stdout[-1500:]     # (the other mode may legitimately fall back when peers cannot be mapped)
