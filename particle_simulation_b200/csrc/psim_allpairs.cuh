@@ -26,7 +26,7 @@ namespace psim {
 // Sharded runs, fused step: where the drift of an owned particle is stored besides this GPU's own buffer — the
 // same record of every other rank's copy of the buffer (peer memory over NVLink, plain stores).  The all-gather of
 // the position shards thereby happens inside the force kernel, block by block, and overlaps its arithmetic; what is
-// left of the collective is a flag per rank (publish_kernel / await_kernel, psim_integrate.cuh).  world == 0: off.
+// left of the collective is a flag per rank (exchange_kernel, psim_integrate.cuh).  world == 0: off.
 constexpr int MAX_PEERS = 16;
 template <class R>
 struct PeerPush {
@@ -58,7 +58,7 @@ __device__ __forceinline__ void store_next(const StepArgs<R>& a, int64_t i, cons
   if (a.peers.world > 1) {
     for (int r = 0; r < a.peers.world; ++r)
       if (r != a.peers.rank) a.peers.pos_nxt[r][i] = x;
-    // No fence here: the flag that tells the peers is raised by publish_kernel, a later kernel of the same stream,
+    // No fence here: the flag that tells the peers is raised by exchange_kernel, a later kernel of the same stream,
     // and a grid's stores (peer memory included) are complete when the grid is — the order every stream-ordered
     // peer-to-peer signal relies on.  A system-scope fence per thread cost 50 us per step on 2 GPUs.
   }

@@ -210,7 +210,7 @@ class SimT final : public psim_sim {
   ncclComm_t comm = nullptr;
   // Peer stores (PeerPush, psim_allpairs.cuh): every rank's position buffers, trigger table and flag array, mapped
   // through CUDA IPC at create; the fused force kernel then stores x_{n+1} of its particles into all of them and
-  // the per-step all-gather shrinks to publish_kernel + await_kernel.  Off (NCCL all-gather every step) when any
+  // the per-step all-gather shrinks to exchange_kernel.  Off (NCCL all-gather every step) when any
   // rank could not map its peers, with PSIM_GATHER=nccl, and for the unfused drift.
   bool peer_push = false;
   Real4<R>* peer_pos[2][MAX_PEERS] = {};
@@ -644,9 +644,8 @@ class SimT final : public psim_sim {
       PeerMail<R> m;
       m.world = world; m.rank = rank; m.nvals = 2 * ns; m.mine = mine;
       for (int r = 0; r < world; ++r) { m.top2[r] = peer_top2[r]; m.flags[r] = peer_flags[r]; }
-      publish_kernel<R><<<1, 64, 0, stream>>>(m, epoch);
-      await_kernel<<<1, 32, 0, stream>>>(flags, world, rank, epoch, ctrl, kAwaitTimeoutNs);
-      launches += 2;
+      exchange_kernel<R><<<1, 64, 0, stream>>>(m, epoch, flags, ctrl, kAwaitTimeoutNs);
+      ++launches;
     } else if (world > 1) {
       PSIM_NCCL(g_nccl.GroupStart());
       PSIM_NCCL(g_nccl.AllGather(nxt + shard * rank, nxt, (size_t)shard * 4, NcclType<R>::v, comm, stream));

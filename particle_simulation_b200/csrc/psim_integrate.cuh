@@ -14,11 +14,11 @@ struct Control {
   unsigned long long rebuilds;  // times the trigger fired
   unsigned long long n_active;  // scratch for counting
   unsigned ticket;              // last-block hand-over of the top-2 reduction
-  unsigned comm_timeout;        // await_kernel gave up waiting for a peer (sharded runs with peer stores)
+  unsigned comm_timeout;        // exchange_kernel gave up waiting for a peer (sharded runs with peer stores)
 };
 
 // ---- what is left of the per-step collective when the force kernel stores x_{n+1} into the peers' buffers --------
-// (PeerPush, psim_allpairs.cuh).  Launched after the force kernel on the same stream, one small block each.
+// (PeerPush, psim_allpairs.cuh): ONE small block launched after the force kernel on the same stream.
 //
 // publish: this rank's trigger pairs (two largest |displacement| per NB_OF_THREADS slice) go into every peer's
 // table, then every peer's flag for this rank takes the step's epoch.  The force kernel's peer stores precede
@@ -31,7 +31,9 @@ struct PeerMail {
   unsigned long long* flags[MAX_PEERS]; // [r]: rank r's flag array [world]
 };
 template <class R>
-__global__ void __launch_bounds__(64) publish_kernel(const PeerMail<R> m, unsigned long long epoch) {
+__global__ void __launch_bounds__(64) exchange_kernel(const PeerMail<R> m, unsigned long long epoch, const unsigned long long* flags,
+                                                       Control* ctrl, unsigned long long timeout_ns) {
+  // ---- publish ----
   for (int r = 0; r < m.world; ++r) {
     if (r == m.rank) continue;
     for (int k = threadIdx.x; k < m.nvals; k += 64) m.top2[r][(size_t)m.nvals * m.rank + k] = m.mine[k];
@@ -39,18 +41,12 @@ __global__ void __launch_bounds__(64) publish_kernel(const PeerMail<R> m, unsign
   __threadfence_system();
   __syncthreads();
   const int r = threadIdx.x;
-  if (r < m.world && r != m.rank) {
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(m.flags[r] + m.rank), "l"(epoch) : "memory");
-  }
-}
-// await: every peer's flag in THIS rank's array has reached the epoch: its positions and pairs of the step are
-// in this GPU's memory.  Gives up after timeout_ns (a peer died): the host then reports PSIM_ERR_COMM instead of
-// hanging.  Nothing on this GPU waits for this kernel but the stream's own later work.
-__global__ void __launch_bounds__(32) await_kernel(const unsigned long long* flags, int world, int rank,
-                                                    unsigned long long epoch, Control* ctrl, unsigned long long timeout_ns) {
-  const int r = threadIdx.x;
-  if (r >= world || r == rank) return;
+  if (r >= m.world || r == m.rank) return;
+  __threadfence_system();
+  asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(m.flags[r] + m.rank), "l"(epoch) : "memory");
+  // ---- await: peer r's flag in THIS rank's array has reached the epoch: its positions and pairs of the step are
+  // in this GPU's memory.  Gives up after timeout_ns (a peer died): the host then reports PSIM_ERR_COMM instead of
+  // hanging.  Nothing on this GPU waits for this kernel but the stream's own later work. ----
   unsigned long long t0, t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   for (;;) {
