@@ -16,7 +16,10 @@ metric  = pair-interactions/s = N (N-1) ordered pair tests x steps / time,
           whole job over all ranks; timesteps/s is reported
           beside it.
 value   : state resident in HBM, K steps in one psim_advance (fused kernels),
-          CUDA events on the library's stream, max over ranks.
+          CUDA events on the library's stream, max over ranks.  On N > 1 GPUs the
+          positions of a step reach the other ranks as peer-memory stores from
+          inside the force kernel (config.parallelism says how many of the timed
+          steps went that way; PSIM_GATHER=nccl keeps the NCCL all-gather).
 e2e     : the force operator through the C ABI with HOST buffers: every step
           uploads all positions from pinned memory (psim_set_positions),
           evaluates the forces and reads them back (psim_get_aux).
